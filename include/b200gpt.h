@@ -1,0 +1,171 @@
+/* b200gpt — C ABI of the B200-native (sm_100a) quantized-decode hot path of lit-gpt.
+ *
+ * Every entry point takes raw DEVICE pointers, sizes and a CUDA stream (`cudaStream_t` passed as void*),
+ * launches asynchronously on that stream, never allocates, never synchronises, and returns 0 on success.
+ * On failure it returns a B200_ERR_* code and `b200_last_error()` (thread-local) holds the message.
+ * Caller-owned workspaces are sized by the *_workspace_bytes helpers.
+ *
+ * Each function cites the reference interface it replaces (file:line into yuanyaaa/lit-gpt).  The reference's
+ * own quantized arithmetic lives in bitsandbytes==0.41.0 (requirements-all.txt:3) behind
+ * lightning.fabric.plugins.BitsandbytesPrecision (generate/base.py:129-134); see INTEGRATION.md for the
+ * binding a maintainer would add.
+ */
+#ifndef B200GPT_H
+#define B200GPT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200GPT_ABI_VERSION 1
+
+typedef void* b200_stream_t; /* cudaStream_t */
+
+enum b200_status { B200_OK = 0, B200_ERR_INVALID = 1, B200_ERR_CUDA = 2, B200_ERR_UNSUPPORTED = 3 };
+enum b200_dtype { B200_BF16 = 0, B200_F16 = 1, B200_F32 = 2 };
+/* 4-bit weight formats.  NF4/FP4: bitsandbytes block-64 codebooks; INT4: this project's group-128 format
+ * (the reference has no gptq/int4 code). */
+enum b200_qtype { B200_Q_NF4 = 0, B200_Q_FP4 = 1, B200_Q_INT4 = 2 };
+/* GEMV epilogues */
+enum b200_epilogue { B200_EPI_STORE = 0, B200_EPI_RESIDUAL = 1, B200_EPI_SWIGLU = 2 };
+
+/* ---- library ------------------------------------------------------------------------------------------ */
+int b200_abi_version(void);
+const char* b200_last_error(void);
+/* fills SM count and compute capability of the current device */
+int b200_device_info(int* sm_count, int* cc_major, int* cc_minor);
+/* enable/disable programmatic dependent launch (griddepcontrol) on every kernel of the library; returns old value */
+int b200_set_pdl(int enabled);
+/* number of kernels launched by this library since load (the `gpu_launches` evidence of bench.py) */
+int64_t b200_launch_count(void);
+/* tuning override for the fast GEMV: ksteps in {0(auto),1,2,4}, ctas_per_sm in {0(auto),1,2,3,4}; returns 0 */
+int b200_qgemv_tune(int ksteps, int ctas_per_sm, int force_generic);
+
+/* ---- quantisation (replaces bitsandbytes.functional.quantize_4bit / dequantize_4bit reached through
+ *      Params4bit.cuda(); reference call sites generate/base.py:168, generate/tp.py:190, lit_gpt/lora.py:156-160) */
+/* w: `numel` elements of w_dtype, flattened row-major.  packed: (numel+1)/2 bytes, even element in the HIGH
+ * nibble.  absmax: ceil(numel/blocksize) floats.  qtype NF4|FP4.  blocksize must be even (reference uses 64). */
+int b200_quantize_4bit(const void* w, int w_dtype, int64_t numel, int blocksize, int qtype, uint8_t* packed,
+                       float* absmax, b200_stream_t stream);
+int b200_dequantize_4bit(const uint8_t* packed, const float* absmax, int64_t numel, int blocksize, int qtype,
+                         void* out, int out_dtype, b200_stream_t stream);
+/* int4 group-128 (asymmetric RTN, GPTQ storage order): qweight uint32 (N, ceil(K/8)), scales fp16 (N, G),
+ * qzeros uint32 (N, ceil(G/8)), G = ceil(K/group).  `sz` (optional, may be NULL) receives the kernel-side
+ * interleaved half2 {scale, zero} per (row, group) that b200_qgemv consumes. */
+int b200_quantize_int4(const void* w, int w_dtype, int64_t N, int64_t K, int group, uint32_t* qweight,
+                       uint16_t* scales, uint32_t* qzeros, uint32_t* sz, b200_stream_t stream);
+int b200_dequantize_int4(const uint32_t* qweight, const uint16_t* scales, const uint32_t* qzeros, int64_t N,
+                         int64_t K, int group, void* out, int out_dtype, b200_stream_t stream);
+
+/* ---- fused dequant-GEMV, batch 1..16 (replaces bnb.nn.Linear4bit.forward -> kgemm_4bit_inference_naive /
+ *      dequantize+F.linear at lit_gpt/model.py:619,656,713,714,716,519) ------------------------------------
+ * y[b, n] = epilogue( sum_k xin[b, k] * W[n, k] ),  xin = prologue(x):
+ *   prologue: xin = x (+ delta if delta != NULL, rounded to bf16); if x_out != NULL the summed rows are written
+ *             there by one CTA (x_out must not alias x); if norm_weight != NULL xin = RMSNorm(xin) with
+ *             lit_gpt/rmsnorm.py:19-25 rounding (fp32 math, one cast).
+ *   W:        qtype NF4/FP4: `packed` + `absmax` (blocksize 64) as produced by b200_quantize_4bit on the
+ *             row-major (N, K) weight; INT4: qweight + sz.  For B200_EPI_SWIGLU a second matrix (packed2/scale2)
+ *             of the same shape is given and y[b,n] = silu(W·xin) * (W2·xin) with the reference's bf16 rounding
+ *             points (lit_gpt/model.py:712-716).
+ *   epilogue: STORE: y = acc (+ bias); RESIDUAL: y = bf16(acc + bias) + residual (lit_gpt/model.py:591-592).
+ * x, delta, x_out, residual, y, bias, norm_weight are bf16.  batch <= 16.  workspace: b200_qgemv_workspace_bytes().
+ */
+typedef struct b200_qgemv_args {
+  const void* packed;     /* uint8 (NF4/FP4) or uint32 (INT4) */
+  const void* scale;      /* float absmax (NF4/FP4) or half2 sz (INT4) */
+  const void* packed2;    /* second matrix for SWIGLU, else NULL */
+  const void* scale2;
+  int qtype;
+  int blocksize;          /* 64 for NF4/FP4, 128 for INT4 */
+  int64_t N, K;
+  const void* x;          /* (batch, K) bf16 */
+  const void* delta;      /* optional (batch, K) bf16 */
+  void* x_out;            /* optional (batch, K) bf16 */
+  const void* norm_weight;/* optional (K) bf16 */
+  float norm_eps;
+  int batch;
+  int epilogue;
+  const void* bias;       /* optional (N) bf16 */
+  const void* residual;   /* (batch, N) bf16 for EPI_RESIDUAL; may alias y */
+  void* y;                /* (batch, N) bf16 */
+  void* workspace;
+  size_t workspace_bytes;
+} b200_qgemv_args;
+size_t b200_qgemv_workspace_bytes(void);
+int b200_qgemv(const b200_qgemv_args* args, b200_stream_t stream);
+
+/* ---- RMSNorm (replaces lit_gpt/rmsnorm.py:19-25 and the residual add at lit_gpt/model.py:591) ------------
+ * y = RMSNorm(x (+ delta)) * weight; if sum_out != NULL it receives bf16(x + delta).  rows x dim, bf16. */
+int b200_rmsnorm(const void* x, const void* delta, const void* weight, float eps, void* y, void* sum_out,
+                 int64_t rows, int64_t dim, b200_stream_t stream);
+
+/* ---- fused RoPE + KV-cache append + split-K flash-decode attention, T = 1 (replaces lit_gpt/model.py:624-653:
+ *      view/permute/split, apply_rope 767-773, KVCache.forward 788-795, scaled_dot_product_attention 658-665)
+ * qkv: (batch, (n_head + 2*n_groups) * head_size) bf16 in the reference's per-group interleaved order
+ *      [q * q_per_kv, k, v] x n_groups (lit_gpt/model.py:621-628).
+ * cos/sin: the model's own tables (max_seq, rope_n_elem), fp32 or bf16 (never recomputed in-kernel).
+ * pos: device int64/int32 scalar = position being written (input_pos); keys 0..pos are attended.
+ * k_cache/v_cache: (batch, n_groups, max_seq, head_size) bf16, GQA-native (n_groups heads).
+ * out: (batch, n_head * head_size) bf16.  head_size in {64, 128}. */
+typedef struct b200_attn_decode_args {
+  const void* qkv;
+  const void* cos;
+  const void* sin;
+  int table_dtype;   /* B200_F32 or B200_BF16 */
+  int table_preselected; /* 1: cos/sin point at the row already gathered for this token (model.py:505-506); 0: full tables indexed by pos */
+  int rope_n_elem;
+  const void* pos;   /* device scalar */
+  int pos_is_int64;
+  void* k_cache;
+  void* v_cache;
+  void* out;
+  int batch, n_head, n_groups, head_size, max_seq;
+  int num_splits;    /* 0 = auto */
+  void* workspace;
+  size_t workspace_bytes;
+} b200_attn_decode_args;
+size_t b200_attn_decode_workspace_bytes(int batch, int n_head, int head_size, int max_splits);
+int b200_attn_decode(const b200_attn_decode_args* args, b200_stream_t stream);
+
+/* ---- prefill helper: RoPE + KV-cache write for T > 1 tokens at positions pos[0..T) (lit_gpt/model.py:624-649).
+ * table_preselected = 1: cos/sin are (T, rope_n_elem) rows already gathered by input_pos; 0: full tables.
+ * Writes roped q to q_out (batch, n_head, T, head_size) and the roped k / v rows into the GQA-native caches. */
+int b200_rope_kv_append(const void* qkv, const void* cos, const void* sin, int table_dtype, int table_preselected,
+                        int rope_n_elem, const void* pos, int pos_is_int64, void* k_cache, void* v_cache, void* q_out, int batch,
+                        int T, int n_head, int n_groups, int head_size, int max_seq, b200_stream_t stream);
+
+/* ---- small glue kernels so a whole decode step is one CUDA graph of this library's kernels ---------------- */
+/* out[r, :] = wte[idx[r], :]  (lit_gpt/model.py:515) */
+int b200_embedding(const void* idx, int idx_is_int64, const void* wte, void* out, int64_t rows, int64_t dim,
+                   int64_t vocab, b200_stream_t stream);
+/* greedy sampling: token[b] = argmax(logits[b, :vocab]) (generate/base.py:41).  If pos_inout != NULL: pos += 1
+ * (generate/base.py:92) and, if history != NULL, history[pos] = token[0] (the torch.cat of generate/base.py:93
+ * done on the device), so a whole decode loop needs no host round trip. */
+int b200_argmax(const void* logits, int64_t batch, int64_t vocab, int64_t stride, void* token_out,
+                int token_is_int64, void* pos_inout, int pos_is_int64, void* history, int64_t history_len,
+                b200_stream_t stream);
+
+/* ---- prefill GEMM: y (M, N) = x (M, K) · dequant(W)^T, tcgen05/TMEM mainloop (replaces dequantize_4bit +
+ *      F.linear for T > 1 at the same call sites).  Implemented in csrc/qgemm_tcgen05.cu. */
+typedef struct b200_qgemm_args {
+  const void* packed;
+  const void* scale;
+  int qtype;
+  int blocksize;
+  int64_t M, N, K;
+  const void* x; /* (M, K) bf16 */
+  const void* bias;
+  void* y;       /* (M, N) bf16 */
+  void* workspace;
+  size_t workspace_bytes;
+} b200_qgemm_args;
+size_t b200_qgemm_workspace_bytes(int64_t M, int64_t N, int64_t K);
+int b200_qgemm(const b200_qgemm_args* args, b200_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200GPT_H */

@@ -1,0 +1,231 @@
+"""Tensor-level wrappers over the C ABI (``include/b200gpt.h``): argument checking, output allocation, workspaces.
+
+Every function launches on torch's current CUDA stream and never synchronises, so calls are capturable in a CUDA
+graph.  CUDA tensors only — no CPU path exists (``B200Error`` is raised instead).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _cabi as C
+
+QTYPES = {"nf4": C.Q_NF4, "fp4": C.Q_FP4, "int4": C.Q_INT4}
+_workspaces: Dict[Tuple[str, int], torch.Tensor] = {}
+
+
+def _ws(kind: str, device: torch.device, nbytes: int) -> torch.Tensor:
+    """Persistent zero-initialised workspace per (kind, device).  Split-K counters inside are self-cleaning."""
+    key = (kind, device.index if device.index is not None else torch.cuda.current_device())
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < nbytes:
+        if torch.cuda.is_current_stream_capturing():
+            raise C.B200Error(f"workspace '{kind}' must be allocated before CUDA-graph capture (run one eager step first)")
+        buf = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        _workspaces[key] = buf
+    return buf
+
+
+def _bf16c(t: Optional[torch.Tensor], name: str) -> Optional[torch.Tensor]:
+    if t is None:
+        return None
+    if t.dtype != torch.bfloat16:
+        raise C.B200Error(f"{name} must be bfloat16 (got {t.dtype}); the kernels compute in bf16 with fp32 accumulation")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# quantisation
+# ---------------------------------------------------------------------------------------------------------
+def quantize_4bit(w: torch.Tensor, quant_type: str = "nf4", blocksize: int = 64) -> Tuple[torch.Tensor, torch.Tensor]:
+    """-> (packed uint8 [(numel+1)//2, 1], absmax fp32 [ceil(numel/blocksize)]) — bitsandbytes Params4bit layout."""
+    C.require_cuda(w)
+    if w.dtype not in C.DTYPE_CODE:
+        raise C.B200Error(f"quantize_4bit: unsupported dtype {w.dtype}")
+    w = w.contiguous()
+    n = w.numel()
+    packed = torch.empty(((n + 1) // 2, 1), dtype=torch.uint8, device=w.device)
+    absmax = torch.empty(((n + blocksize - 1) // blocksize,), dtype=torch.float32, device=w.device)
+    C.check(C.load().b200_quantize_4bit(w.data_ptr(), C.DTYPE_CODE[w.dtype], n, blocksize, QTYPES[quant_type],
+                                        packed.data_ptr(), absmax.data_ptr(), C.stream_ptr(w.device)), "quantize_4bit")
+    return packed, absmax
+
+
+def dequantize_4bit(packed: torch.Tensor, absmax: torch.Tensor, shape, dtype: torch.dtype = torch.bfloat16,
+                    quant_type: str = "nf4", blocksize: int = 64) -> torch.Tensor:
+    C.require_cuda(packed, absmax)
+    out = torch.empty(tuple(shape), dtype=dtype, device=packed.device)
+    C.check(C.load().b200_dequantize_4bit(packed.data_ptr(), absmax.data_ptr(), out.numel(), blocksize, QTYPES[quant_type],
+                                          out.data_ptr(), C.DTYPE_CODE[dtype], C.stream_ptr(packed.device)), "dequantize_4bit")
+    return out
+
+
+def quantize_int4(w: torch.Tensor, group: int = 128):
+    """-> (qweight uint32-as-int32 (N, ceil(K/8)), scales fp16 (N, G), qzeros int32 (N, ceil(G/8)), sz int32 (N, G))."""
+    C.require_cuda(w)
+    if w.dim() != 2:
+        raise C.B200Error("quantize_int4 expects a 2-D (out_features, in_features) weight")
+    w = w.contiguous()
+    N, K = w.shape
+    G = (K + group - 1) // group
+    qweight = torch.empty((N, (K + 7) // 8), dtype=torch.int32, device=w.device)
+    scales = torch.empty((N, G), dtype=torch.float16, device=w.device)
+    qzeros = torch.empty((N, (G + 7) // 8), dtype=torch.int32, device=w.device)
+    sz = torch.empty((N, G), dtype=torch.int32, device=w.device)
+    C.check(C.load().b200_quantize_int4(w.data_ptr(), C.DTYPE_CODE[w.dtype], N, K, group, qweight.data_ptr(), scales.data_ptr(),
+                                        qzeros.data_ptr(), sz.data_ptr(), C.stream_ptr(w.device)), "quantize_int4")
+    return qweight, scales, qzeros, sz
+
+
+def dequantize_int4(qweight, scales, qzeros, K: int, group: int = 128, dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    C.require_cuda(qweight, scales, qzeros)
+    N = qweight.shape[0]
+    out = torch.empty((N, K), dtype=dtype, device=qweight.device)
+    C.check(C.load().b200_dequantize_int4(qweight.data_ptr(), scales.data_ptr(), qzeros.data_ptr(), N, K, group, out.data_ptr(),
+                                          C.DTYPE_CODE[dtype], C.stream_ptr(qweight.device)), "dequantize_int4")
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# fused dequant-GEMV (batch <= 16)
+# ---------------------------------------------------------------------------------------------------------
+def qgemv(x: torch.Tensor, packed: torch.Tensor, scale: torch.Tensor, N: int, K: int, quant_type: str = "nf4",
+          blocksize: int = 64, *, bias: Optional[torch.Tensor] = None, delta: Optional[torch.Tensor] = None,
+          x_out: Optional[torch.Tensor] = None, norm_weight: Optional[torch.Tensor] = None, norm_eps: float = 1e-5,
+          residual: Optional[torch.Tensor] = None, packed2: Optional[torch.Tensor] = None,
+          scale2: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = epilogue(prologue(x) @ dequant(W).T); see b200_qgemv in include/b200gpt.h.  x: (..., K) with <= 16 rows."""
+    C.require_cuda(x, packed, scale)
+    x = _bf16c(x, "x")
+    lead = x.shape[:-1]
+    batch = x.numel() // K
+    if x.shape[-1] != K:
+        raise C.B200Error(f"qgemv: x has {x.shape[-1]} features, weight expects {K}")
+    epilogue = C.EPI_SWIGLU if packed2 is not None else (C.EPI_RESIDUAL if residual is not None else C.EPI_STORE)
+    y = out if out is not None else torch.empty((*lead, N), dtype=torch.bfloat16, device=x.device)
+    nbytes = C.load().b200_qgemv_workspace_bytes()
+    ws = _ws("qgemv", x.device, nbytes)
+    delta, residual, bias, norm_weight = _bf16c(delta, "delta"), _bf16c(residual, "residual"), _bf16c(bias, "bias"), _bf16c(norm_weight, "norm_weight")
+    args = C.QGemvArgs(
+        packed=packed.data_ptr(), scale=scale.data_ptr(), packed2=C.ptr(packed2), scale2=C.ptr(scale2),
+        qtype=QTYPES[quant_type], blocksize=blocksize, N=N, K=K, x=x.data_ptr(), delta=C.ptr(delta), x_out=C.ptr(x_out),
+        norm_weight=C.ptr(norm_weight), norm_eps=norm_eps, batch=batch, epilogue=epilogue, bias=C.ptr(bias),
+        residual=C.ptr(residual), y=y.data_ptr(), workspace=ws.data_ptr(), workspace_bytes=ws.numel())
+    C.check(C.load().b200_qgemv(ctypes.byref(args), C.stream_ptr(x.device)), "qgemv")
+    return y
+
+
+# ---------------------------------------------------------------------------------------------------------
+# norm / embedding / argmax
+# ---------------------------------------------------------------------------------------------------------
+def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float = 1e-5, delta: Optional[torch.Tensor] = None,
+            sum_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    C.require_cuda(x, weight)
+    x, weight, delta = _bf16c(x, "x"), _bf16c(weight, "weight"), _bf16c(delta, "delta")
+    dim = x.shape[-1]
+    y = torch.empty_like(x)
+    C.check(C.load().b200_rmsnorm(x.data_ptr(), C.ptr(delta), weight.data_ptr(), eps, y.data_ptr(), C.ptr(sum_out),
+                                  x.numel() // dim, dim, C.stream_ptr(x.device)), "rmsnorm")
+    return y
+
+
+def embedding(idx: torch.Tensor, wte: torch.Tensor) -> torch.Tensor:
+    C.require_cuda(idx, wte)
+    wte = _bf16c(wte, "wte")
+    if idx.dtype not in (torch.int64, torch.int32):
+        raise C.B200Error(f"embedding: idx must be int32/int64 (got {idx.dtype})")
+    idx = idx.contiguous()
+    out = torch.empty((*idx.shape, wte.shape[1]), dtype=torch.bfloat16, device=wte.device)
+    C.check(C.load().b200_embedding(idx.data_ptr(), int(idx.dtype == torch.int64), wte.data_ptr(), out.data_ptr(), idx.numel(),
+                                    wte.shape[1], wte.shape[0], C.stream_ptr(wte.device)), "embedding")
+    return out
+
+
+def argmax_(logits: torch.Tensor, token_out: torch.Tensor, pos_inout: Optional[torch.Tensor] = None, vocab: Optional[int] = None,
+            history: Optional[torch.Tensor] = None) -> None:
+    """token_out[b] = argmax(logits[b, :vocab]); optionally pos_inout[0] += 1 and history[pos] = token (on device)."""
+    if history is not None and history.dtype != token_out.dtype:
+        raise C.B200Error("argmax_: history must have the dtype of token_out")
+    C.require_cuda(logits, token_out)
+    logits = _bf16c(logits, "logits")
+    V = logits.shape[-1]
+    batch = logits.numel() // V
+    C.check(C.load().b200_argmax(logits.data_ptr(), batch, vocab or V, V, token_out.data_ptr(), int(token_out.dtype == torch.int64),
+                                 C.ptr(pos_inout), int(pos_inout is not None and pos_inout.dtype == torch.int64),
+                                 C.ptr(history), 0 if history is None else history.numel(),
+                                 C.stream_ptr(logits.device)), "argmax")
+
+
+# ---------------------------------------------------------------------------------------------------------
+# attention
+# ---------------------------------------------------------------------------------------------------------
+def _table_code(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return C.F32
+    if t.dtype == torch.bfloat16:
+        return C.BF16
+    raise C.B200Error(f"cos/sin tables must be fp32 or bf16 (got {t.dtype})")
+
+
+def attn_decode(qkv: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, pos: torch.Tensor, k_cache: torch.Tensor,
+                v_cache: torch.Tensor, n_head: int, n_groups: int, head_size: int, rope_n_elem: int,
+                num_splits: int = 0, table_preselected: bool = False) -> torch.Tensor:
+    """Fused RoPE + cache append + split-K decode attention for one token per sequence.
+
+    qkv (B, 1, (H+2G)*hs) or (B, (H+2G)*hs); cos/sin: the model's FULL tables (max_seq, rope_n_elem); pos: device int
+    scalar tensor (input_pos); caches (B, G, max_seq, hs) bf16, updated in place.  Returns (B, H*hs)."""
+    C.require_cuda(qkv, cos, sin, pos, k_cache, v_cache)
+    qkv = _bf16c(qkv, "qkv")
+    B = k_cache.shape[0]
+    max_seq = k_cache.shape[2]
+    if k_cache.dtype != torch.bfloat16 or not k_cache.is_contiguous() or not v_cache.is_contiguous():
+        raise C.B200Error("kv cache must be contiguous bfloat16 (B, n_query_groups, max_seq, head_size)")
+    if qkv.numel() != B * (n_head + 2 * n_groups) * head_size:
+        raise C.B200Error("attn_decode: qkv does not hold exactly one token per cached sequence")
+    if pos.dtype not in (torch.int64, torch.int32) or pos.numel() != 1:
+        raise C.B200Error("attn_decode: pos must be a single int32/int64 device scalar")
+    cos, sin = cos.contiguous(), sin.contiguous()
+    out = torch.empty((B, n_head * head_size), dtype=torch.bfloat16, device=qkv.device)
+    lib = C.load()
+    max_splits = 64
+    ws = _ws("attn", qkv.device, lib.b200_attn_decode_workspace_bytes(B, n_head, head_size, max_splits))
+    args = C.AttnDecodeArgs(
+        qkv=qkv.data_ptr(), cos=cos.data_ptr(), sin=sin.data_ptr(), table_dtype=_table_code(cos), table_preselected=int(table_preselected), rope_n_elem=rope_n_elem,
+        pos=pos.data_ptr(), pos_is_int64=int(pos.dtype == torch.int64), k_cache=k_cache.data_ptr(), v_cache=v_cache.data_ptr(),
+        out=out.data_ptr(), batch=B, n_head=n_head, n_groups=n_groups, head_size=head_size, max_seq=max_seq,
+        num_splits=num_splits, workspace=ws.data_ptr(), workspace_bytes=ws.numel())
+    C.check(lib.b200_attn_decode(ctypes.byref(args), C.stream_ptr(qkv.device)), "attn_decode")
+    return out
+
+
+def rope_kv_append(qkv: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, pos: torch.Tensor, k_cache: torch.Tensor,
+                   v_cache: torch.Tensor, n_head: int, n_groups: int, head_size: int, rope_n_elem: int,
+                   table_preselected: bool = False) -> torch.Tensor:
+    """Prefill: RoPE q/k for T tokens at positions pos[0..T), write k/v into the GQA-native caches, return roped q
+    as (B, H, T, hs)."""
+    C.require_cuda(qkv, cos, sin, pos, k_cache, v_cache)
+    qkv = _bf16c(qkv, "qkv")
+    B, T = qkv.shape[0], qkv.shape[1]
+    if pos.numel() != T:
+        raise C.B200Error("rope_kv_append: pos must have one entry per token")
+    cos, sin, pos = cos.contiguous(), sin.contiguous(), pos.contiguous()
+    q = torch.empty((B, n_head, T, head_size), dtype=torch.bfloat16, device=qkv.device)
+    C.check(C.load().b200_rope_kv_append(qkv.data_ptr(), cos.data_ptr(), sin.data_ptr(), _table_code(cos), int(table_preselected), rope_n_elem,
+                                         pos.data_ptr(), int(pos.dtype == torch.int64), k_cache.data_ptr(), v_cache.data_ptr(),
+                                         q.data_ptr(), B, T, n_head, n_groups, head_size, k_cache.shape[2],
+                                         C.stream_ptr(qkv.device)), "rope_kv_append")
+    return q
+
+
+def set_pdl(enabled: bool) -> bool:
+    return bool(C.load().b200_set_pdl(int(enabled)))
+
+
+def launch_count() -> int:
+    return int(C.load().b200_launch_count())
+
+
+def qgemv_tune(ksteps: int = 0, ctas_per_sm: int = 0, force_generic: bool = False) -> None:
+    C.load().b200_qgemv_tune(ksteps, ctas_per_sm, int(force_generic))

@@ -1,0 +1,427 @@
+"""Decoder-only transformer with the reference's public surface (``lit_gpt/model.py:445-804``): ``GPT``, ``Block``,
+``CausalSelfAttention``, ``GptNeoxMLP``, ``LLaMAMLP``, ``KVCache``, ``build_rope_cache``, ``apply_rope``,
+``build_mask_cache`` — same constructor signatures, parameter names (state-dict compatible) and error behaviour.
+
+What differs is what runs underneath on a B200:
+
+* CUDA + bf16: attention goes through the library's fused kernels (RoPE + KV append + split-K flash-decode for T = 1,
+  RoPE + KV append then SDPA for prefill) over a GQA-NATIVE cache (``n_query_groups`` heads, not ``n_head``).
+* When every Linear is a quantized ``QLinear`` and the block is Llama-shaped, a decode step (T = 1) does not walk the
+  module tree at all: ``GPT._fused_decode`` issues 5 kernels per block (norm folded into GEMV prologues, residual and
+  SwiGLU into epilogues), all capturable in one CUDA graph.
+* Anything else (fp32 / CPU, e.g. BASELINE config 1) runs the reference formulation in plain torch, so results are
+  identical to the reference there.
+"""
+from __future__ import annotations
+
+import math
+from typing import Any, List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import kernels as K
+from .config import Config
+from .quant import QLinear
+
+FUSED_HEAD_SIZES = (64, 128)
+
+
+class GPT(nn.Module):
+    def __init__(self, config: Config) -> None:
+        super().__init__()
+        assert config.padded_vocab_size is not None
+        self.config = config
+        self.lm_head = nn.Linear(config.n_embd, config.padded_vocab_size, bias=config.lm_head_bias)
+        self.transformer = nn.ModuleDict(
+            dict(
+                wte=nn.Embedding(config.padded_vocab_size, config.n_embd),
+                h=nn.ModuleList(Block(config) for _ in range(config.n_layer)),
+                ln_f=config.norm_class(config.n_embd, eps=config.norm_eps),
+            )
+        )
+        self.max_seq_length = self.config.block_size
+        self.mask_cache: Optional[torch.Tensor] = None
+        # tensor-parallel state, set by generate.tp.tensor_parallel (None = single GPU)
+        self.tp_group: Any = None
+        self.tp_world_size: int = 1
+
+    @property
+    def max_seq_length(self) -> int:
+        return self._max_seq_length
+
+    @max_seq_length.setter
+    def max_seq_length(self, value: int) -> None:
+        """Smaller than block_size to bound cache memory (reference model.py:466-484)."""
+        if value > self.config.block_size:
+            raise ValueError(f"Cannot attend to {value}, block size is only {self.config.block_size}")
+        self._max_seq_length = value
+        if not hasattr(self, "cos"):
+            cos, sin = self.rope_cache()
+            self.register_buffer("cos", cos, persistent=False)
+            self.register_buffer("sin", sin, persistent=False)
+        elif value != self.cos.size(0):
+            self.cos, self.sin = self.rope_cache(device=self.cos.device)
+
+    def reset_parameters(self) -> None:
+        self.cos, self.sin = self.rope_cache()
+
+    def _init_weights(self, module: nn.Module) -> None:
+        """`gpt.apply(gpt._init_weights)`: N(0, 0.02) for Linear / Embedding weights, zero biases."""
+        if isinstance(module, (nn.Linear, QLinear)):
+            if module.weight.is_floating_point():
+                torch.nn.init.normal_(module.weight, mean=0.0, std=0.02)
+            if module.bias is not None:
+                torch.nn.init.zeros_(module.bias)
+        elif isinstance(module, nn.Embedding):
+            torch.nn.init.normal_(module.weight, mean=0.0, std=0.02)
+
+    def forward(self, idx: torch.Tensor, input_pos: Optional[torch.Tensor] = None) -> torch.Tensor:
+        T = idx.size(1)
+        if self.max_seq_length < T:
+            raise ValueError(f"Cannot forward sequence of length {T}, max seq length is only {self.max_seq_length}.")
+
+        if input_pos is not None:
+            if self.mask_cache is None:
+                raise TypeError("You need to call `gpt.set_kv_cache()`")
+            if T == 1 and input_pos.numel() == 1 and self.fused_decode_ready(idx):
+                return self._fused_decode(idx, input_pos)
+            cos = self.cos.index_select(0, input_pos)
+            sin = self.sin.index_select(0, input_pos)
+            mask = self.mask_cache.index_select(2, input_pos)
+        else:
+            cos = self.cos[:T]
+            sin = self.sin[:T]
+            mask = None
+
+        x = self.transformer.wte(idx)
+        for block in self.transformer.h:
+            x = block(x, cos, sin, mask, input_pos)
+        x = self.transformer.ln_f(x)
+        return self.lm_head(x)
+
+    @classmethod
+    def from_name(cls, name: str, **kwargs: Any) -> "GPT":
+        return cls(Config.from_name(name, **kwargs))
+
+    def rope_cache(self, device: Optional[torch.device] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+        return build_rope_cache(
+            seq_len=self.max_seq_length,
+            n_elem=self.config.rope_n_elem,
+            device=device,
+            condense_ratio=self.config.rope_condense_ratio,
+            base=self.config.rope_base,
+        )
+
+    def set_kv_cache(self, batch_size: int, rope_cache_length: Optional[int] = None,
+                     device: Optional[torch.device] = None, dtype: Optional[torch.dtype] = None) -> None:
+        if rope_cache_length is None:
+            rope_cache_length = self.cos.size(-1)
+        max_seq_length = self.max_seq_length
+        for block in self.transformer.h:
+            block.attn.kv_cache = block.attn.build_kv_cache(batch_size, max_seq_length, rope_cache_length, device, dtype)
+        if self.mask_cache is None or self.mask_cache.size(3) != max_seq_length:
+            self.mask_cache = build_mask_cache(max_seq_length, device)
+        self._fused_plan = None
+
+    def clear_kv_cache(self) -> None:
+        self.mask_cache = None
+        for block in self.transformer.h:
+            block.attn.kv_cache = None
+        self._fused_plan = None
+
+    # ------------------------------------------------------------------------------------------------------
+    # fused decode step
+    # ------------------------------------------------------------------------------------------------------
+    _fused_plan: Optional[bool] = None
+
+    def _apply(self, fn, recurse: bool = True):
+        self._fused_plan = None  # device moves quantize the Linears: re-plan on the next forward
+        return super()._apply(fn, recurse)
+
+    def fused_decode_ready(self, idx: Optional[torch.Tensor] = None) -> bool:
+        """True when a T=1 step can run as the 5-kernels-per-block fused chain (see module docstring)."""
+        if idx is not None and not idx.is_cuda:
+            return False
+        if self._fused_plan is None:
+            self._fused_plan = self._check_fused()
+        return self._fused_plan
+
+    def _check_fused(self) -> bool:
+        c = self.config
+        if c._norm_class != "RMSNorm" or c._mlp_class != "LLaMAMLP" or c.parallel_residual or c.shared_attention_norm:
+            return False
+        if c.n_expert or c.head_size not in FUSED_HEAD_SIZES or c.rope_n_elem % 2:
+            return False
+        wte = self.transformer.wte.weight
+        if not wte.is_cuda or wte.dtype != torch.bfloat16:
+            return False
+
+        def ok(lin: nn.Module) -> bool:
+            return isinstance(lin, QLinear) and lin.is_quantized and lin.weight.is_cuda and lin.bias is None
+
+        for block in self.transformer.h:
+            a, m = block.attn, block.mlp
+            if not (ok(a.attn) and ok(a.proj) and ok(m.fc_1) and ok(m.fc_2) and ok(m.proj)):
+                return False
+            if m.fc_1.quant_type != m.fc_2.quant_type:
+                return False
+            if not isinstance(a.kv_cache, KVCache) or not a.kv_cache.gqa_native:
+                return False
+            if block.norm_1.weight.dtype != torch.bfloat16 or block.norm_2.weight.dtype != torch.bfloat16:
+                return False
+            # forward hooks other than our own TP marker would be bypassed by the fused chain
+            if (a._forward_hooks or m._forward_hooks) and self.tp_world_size == 1:
+                return False
+        return ok(self.lm_head) and self.transformer.ln_f.weight.dtype == torch.bfloat16
+
+    def _all_reduce(self, t: torch.Tensor) -> torch.Tensor:
+        import torch.distributed as dist
+
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.tp_group)  # NCCL over NVLink; sums row-parallel partials
+        return t
+
+    def _fused_decode(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
+        """One token per sequence.  Same math as Block.forward / CausalSelfAttention.forward / LLaMAMLP.forward of
+        the reference (model.py:572-593, 609-656, 712-716) with identical bf16 rounding points."""
+        c = self.config
+        B = idx.size(0)
+        tp = self.tp_world_size > 1
+        x = K.embedding(idx.view(B), self.transformer.wte.weight)  # (B, d_full)
+        delta: Optional[torch.Tensor] = None
+        eps = c.norm_eps
+
+        def lin(q: QLinear, inp: torch.Tensor, **kw: Any) -> torch.Tensor:
+            return K.qgemv(inp, q.weight.data, q.scale, q.out_features, q.in_features, q.quant_type, q.blocksize, **kw)
+
+        for block in self.transformer.h:
+            a, m, cache = block.attn, block.mlp, block.attn.kv_cache
+            if delta is not None:  # TP: the all-reduced branch output is added in the next prologue
+                x_new = torch.empty_like(x)
+                qkv = lin(a.attn, x, delta=delta, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps)
+                x = x_new
+            else:
+                qkv = lin(a.attn, x, norm_weight=block.norm_1.weight, norm_eps=eps)
+            y = K.attn_decode(qkv, self.cos, self.sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups,
+                              c.head_size, c.rope_n_elem)
+            if tp:
+                h = self._all_reduce(lin(a.proj, y))
+                x_new = torch.empty_like(x)
+                act = lin(m.fc_1, x, delta=h, x_out=x_new, norm_weight=block.norm_2.weight, norm_eps=eps,
+                          packed2=m.fc_2.weight.data, scale2=m.fc_2.scale)
+                x = x_new
+                delta = self._all_reduce(lin(m.proj, act))
+            else:
+                x = lin(a.proj, y, residual=x)
+                act = lin(m.fc_1, x, norm_weight=block.norm_2.weight, norm_eps=eps, packed2=m.fc_2.weight.data,
+                          scale2=m.fc_2.scale)
+                x = lin(m.proj, act, residual=x)
+        logits = lin(self.lm_head, x, delta=delta, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+        return logits.view(B, 1, -1)
+
+
+class Block(nn.Module):
+    def __init__(self, config: Config) -> None:
+        super().__init__()
+        self.norm_1 = config.norm_class(config.n_embd, eps=config.norm_eps)
+        self.attn = CausalSelfAttention(config)
+        self.norm_2 = None if config.shared_attention_norm else config.norm_class(config.n_embd, eps=config.norm_eps)
+        self.mlp = config.mlp_class(config)
+        self.config = config
+
+    def forward(self, x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, mask: Optional[torch.Tensor] = None,
+                input_pos: Optional[torch.Tensor] = None) -> torch.Tensor:
+        n_1 = self.norm_1(x)
+        h = self.attn(n_1, cos, sin, mask, input_pos)
+        if self.config.parallel_residual:
+            n_2 = n_1 if self.config.shared_attention_norm else self.norm_2(x)
+            x = self.mlp(n_2) + h + x
+        else:
+            if self.config.shared_attention_norm:
+                raise NotImplementedError(
+                    "No checkpoint amongst the ones we support uses this configuration"
+                    " (non-parallel residual and shared attention norm)."
+                )
+            x = h + x
+            x = self.mlp(self.norm_2(x)) + x
+        return x
+
+
+class CausalSelfAttention(nn.Module):
+    def __init__(self, config: Config) -> None:
+        super().__init__()
+        shape = (config.n_head + 2 * config.n_query_groups) * config.head_size
+        # fused q/k/v projection; rows are interleaved per query group: [q * q_per_kv, k, v] x n_query_groups
+        self.attn = nn.Linear(config.n_embd, shape, bias=config.bias)
+        self.proj = nn.Linear(config.n_embd, config.n_embd, bias=config.bias)
+        self.kv_cache: Optional[KVCache] = None
+        self.config = config
+
+    def forward(self, x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, mask: Optional[torch.Tensor] = None,
+                input_pos: Optional[torch.Tensor] = None) -> torch.Tensor:
+        B, T, C = x.size()
+        c = self.config
+        qkv = self.attn(x)
+
+        if input_pos is not None:
+            if not isinstance(self.kv_cache, KVCache):
+                raise TypeError("You need to call `gpt.set_kv_cache()`")
+            if self.kv_cache.gqa_native:
+                if not (qkv.is_cuda and qkv.dtype == torch.bfloat16):
+                    raise RuntimeError("the GQA-native kv cache is driven by the CUDA bf16 kernels only")
+                return self.proj(self._fused_cached_attention(qkv, cos, sin, mask, input_pos))
+
+        # ---- reference formulation (model.py:621-653) ---------------------------------------------------
+        q_per_kv = c.n_head // c.n_query_groups
+        total_qkv = q_per_kv + 2
+        qkv = qkv.view(B, T, c.n_query_groups, total_qkv, c.head_size).permute(0, 2, 3, 1, 4)
+        q, k, v = qkv.split((q_per_kv, 1, 1), dim=2)
+        if c.n_query_groups != c.n_head and (input_pos is None or c.n_query_groups != 1):
+            k = k.expand(B, c.n_query_groups, q_per_kv, T, c.head_size)
+            v = v.expand(B, c.n_query_groups, q_per_kv, T, c.head_size)
+        q = q.reshape(B, -1, T, c.head_size)
+        k = k.reshape(B, -1, T, c.head_size)
+        v = v.reshape(B, -1, T, c.head_size)
+        q_roped = apply_rope(q[..., : c.rope_n_elem], cos, sin)
+        k_roped = apply_rope(k[..., : c.rope_n_elem], cos, sin)
+        q = torch.cat((q_roped, q[..., c.rope_n_elem :]), dim=-1)
+        k = torch.cat((k_roped, k[..., c.rope_n_elem :]), dim=-1)
+        if input_pos is not None:
+            k, v = self.kv_cache(input_pos, k, v)
+        y = self.scaled_dot_product_attention(q, k, v, mask)
+        y = y.reshape(B, T, c.n_embd)
+        return self.proj(y)
+
+    def _fused_cached_attention(self, qkv: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor,
+                                mask: Optional[torch.Tensor], input_pos: torch.Tensor) -> torch.Tensor:
+        c, cache = self.config, self.kv_cache
+        B, T, _ = qkv.shape
+        if T == 1:
+            y = K.attn_decode(qkv, cos, sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups, c.head_size,
+                              c.rope_n_elem, table_preselected=True)
+            return y.view(B, 1, c.n_head * c.head_size)
+        q = K.rope_kv_append(qkv, cos, sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups, c.head_size,
+                             c.rope_n_elem, table_preselected=True)
+        scale = 1.0 / math.sqrt(c.head_size)
+        y = F.scaled_dot_product_attention(q, cache.k, cache.v, attn_mask=mask, dropout_p=0.0, scale=scale,
+                                           enable_gqa=c.n_query_groups != c.n_head)
+        return y.transpose(1, 2).reshape(B, T, c.n_head * c.head_size)
+
+    def scaled_dot_product_attention(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
+                                     mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        scale = 1.0 / math.sqrt(self.config.head_size)
+        y = F.scaled_dot_product_attention(q, k, v, attn_mask=mask, dropout_p=0.0, scale=scale, is_causal=mask is None)
+        return y.transpose(1, 2)
+
+    def build_kv_cache(self, batch_size: int, max_seq_length: int, rope_cache_length: Optional[int] = None,
+                       device: Optional[torch.device] = None, dtype: Optional[torch.dtype] = None) -> "KVCache":
+        c = self.config
+        probe = torch.empty(0, device=device, dtype=dtype)
+        native = (probe.is_cuda and probe.dtype == torch.bfloat16 and c.head_size in FUSED_HEAD_SIZES
+                  and c.rope_n_elem % 2 == 0 and (rope_cache_length is None or rope_cache_length == c.rope_n_elem))
+        if native:  # GQA-native: n_query_groups heads (the reference stores n_head)
+            shape = (batch_size, c.n_query_groups, max_seq_length, c.head_size)
+            return KVCache(shape, shape, device=device, dtype=dtype, gqa_native=True)
+        heads = 1 if c.n_query_groups == 1 else c.n_head
+        v_shape = (batch_size, heads, max_seq_length, c.head_size)
+        if rope_cache_length is None:
+            if c.rotary_percentage != 1.0:
+                raise TypeError("Please pass the `rope_cache_length=gpt.cos.size(-1)` value")
+            k_shape = v_shape
+        else:
+            k_shape = (batch_size, heads, max_seq_length, rope_cache_length + c.head_size - c.rope_n_elem)
+        return KVCache(k_shape, v_shape, device=device, dtype=dtype)
+
+
+class GptNeoxMLP(nn.Module):
+    def __init__(self, config: Config) -> None:
+        super().__init__()
+        self.fc = nn.Linear(config.n_embd, config.intermediate_size, bias=config.bias)
+        self.proj = nn.Linear(config.intermediate_size, config.n_embd, bias=config.bias)
+        self.config = config
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x = self.fc(x)
+        x = F.gelu(x, approximate=self.config.gelu_approximate)
+        return self.proj(x)
+
+
+class LLaMAMLP(nn.Module):
+    def __init__(self, config: Config) -> None:
+        super().__init__()
+        self.fc_1 = nn.Linear(config.n_embd, config.intermediate_size, bias=config.bias)
+        self.fc_2 = nn.Linear(config.n_embd, config.intermediate_size, bias=config.bias)
+        self.proj = nn.Linear(config.intermediate_size, config.n_embd, bias=config.bias)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        f1, f2 = self.fc_1, self.fc_2
+        rows = x.numel() // x.size(-1)
+        if (isinstance(f1, QLinear) and isinstance(f2, QLinear) and f1.is_quantized and f2.is_quantized and x.is_cuda
+                and x.dtype == torch.bfloat16 and rows <= 16 and f1.bias is None and f2.bias is None
+                and f1.quant_type == f2.quant_type):
+            # gate and up projections + SwiGLU in one pass over both weight matrices
+            act = K.qgemv(x, f1.weight.data, f1.scale, f1.out_features, f1.in_features, f1.quant_type, f1.blocksize,
+                          packed2=f2.weight.data, scale2=f2.scale)
+            return self.proj(act)
+        x_fc_1 = self.fc_1(x)
+        x_fc_2 = self.fc_2(x)
+        x = F.silu(x_fc_1) * x_fc_2
+        return self.proj(x)
+
+
+class LLaMAMoE(nn.Module):
+    """Mixtral-style routing is outside the hot path (no BASELINE config uses it); kept so that
+    ``config._mlp_class = "LLaMAMoE"`` resolves and fails with a clear message."""
+
+    def __init__(self, config: Config) -> None:
+        super().__init__()
+        raise NotImplementedError("LLaMAMoE is out of scope for the B200 quantized-decode hot path")
+
+
+def build_rope_cache(seq_len: int, n_elem: int, device: Optional[torch.device] = None, base: int = 10000,
+                     condense_ratio: int = 1) -> Tuple[torch.Tensor, torch.Tensor]:
+    """cos/sin tables (seq_len, n_elem).  Positions are an integer arange divided by a python int, i.e. they take
+    the DEFAULT float dtype exactly as the reference does (model.py:759) — the kernels consume these
+    tables and never recompute angles."""
+    theta = 1.0 / (base ** (torch.arange(0, n_elem, 2, device=device).float() / n_elem))
+    seq_idx = torch.arange(seq_len, device=device) / condense_ratio
+    idx_theta = torch.outer(seq_idx, theta).repeat(1, 2)
+    return torch.cos(idx_theta), torch.sin(idx_theta)
+
+
+def apply_rope(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.Tensor:
+    head_size = x.size(-1)
+    x1 = x[..., : head_size // 2]
+    x2 = x[..., head_size // 2 :]
+    rotated = torch.cat((-x2, x1), dim=-1)
+    roped = (x * cos) + (rotated * sin)
+    return roped.to(dtype=x.dtype)
+
+
+class KVCache(nn.Module):
+    def __init__(self, k_shape: Tuple[int, int, int, int], v_shape: Tuple[int, int, int, int],
+                 device: Optional[torch.device] = None, dtype: Optional[torch.dtype] = None,
+                 gqa_native: bool = False) -> None:
+        super().__init__()
+        self.register_buffer("k", torch.zeros(k_shape, device=device, dtype=dtype), persistent=False)
+        self.register_buffer("v", torch.zeros(v_shape, device=device, dtype=dtype), persistent=False)
+        self.gqa_native = gqa_native
+
+    def forward(self, input_pos: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        if self.gqa_native:
+            raise RuntimeError("a GQA-native cache is updated inside the fused attention kernels")
+        self.k = self.k.to(k.dtype)
+        self.v = self.v.to(v.dtype)
+        k = self.k.index_copy_(2, input_pos, k)
+        v = self.v.index_copy_(2, input_pos, v)
+        return k, v
+
+    def reset_parameters(self) -> None:
+        torch.nn.init.zeros_(self.k)
+        torch.nn.init.zeros_(self.v)
+
+
+def build_mask_cache(max_seq_length: int, device: Optional[torch.device] = None) -> torch.Tensor:
+    ones = torch.ones((max_seq_length, max_seq_length), device=device, dtype=torch.bool)
+    return torch.tril(ones).unsqueeze(0).unsqueeze(0)

@@ -1,0 +1,257 @@
+"""Weight-only quantized Linear and the precision plugin that installs it.
+
+Replaces ``lightning.fabric.plugins.BitsandbytesPrecision`` + ``bitsandbytes.nn.Linear4bit`` as used by the
+reference (generate/base.py:129-134,151,168; generate/tp.py:127-134,171,190):
+
+* ``QuantPrecision(mode, dtype)`` mirrors ``BitsandbytesPrecision(quantize[4:], dtype)``: ``convert_module`` swaps
+  every ``nn.Linear`` (``lm_head`` included) for ``QLinear``; ``module_init_context`` makes ``nn.Linear`` construct
+  ``QLinear`` directly (the ``fabric.init_module`` path).
+* ``QLinear`` keeps ``weight`` / ``bias`` / ``in_features`` / ``out_features``.  While unquantized it tolerates
+  ``linear.weight.data = shard`` and attribute edits (generate/tp.py:37-45); it quantizes ON THE GPU when the module
+  is moved to a CUDA device, or when a full-precision ``weight`` arrives through ``load_state_dict`` on a module that
+  already lives on CUDA (lit_gpt/utils.py:354-356).  After that ``weight`` is the packed uint8 ``(numel/2, 1)`` tensor
+  and ``quant_state`` is the bitsandbytes-0.41 list form ``[absmax, shape, dtype, blocksize, None, quant_type, data_type]``
+  (lit_gpt/utils.py:85-87 reads index 1).
+* forward: <= 16 activation rows -> the fused dequant-GEMV; more rows (prefill) -> the prefill GEMM.
+
+There is no CPU implementation: calling a QLinear that is not on CUDA raises.
+"""
+from __future__ import annotations
+
+import contextlib
+from typing import Any, Iterator, List, Optional, Set
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import kernels as K
+from ._cabi import B200Error
+
+MODES = ("nf4", "nf4-dq", "fp4", "fp4-dq", "int8", "int4")
+GEMV_MAX_ROWS = 16
+
+
+class QLinear(nn.Module):
+    def __init__(self, in_features: int, out_features: int, bias: bool = True, device=None, dtype=None,
+                 mode: str = "nf4", compute_dtype: torch.dtype = torch.bfloat16) -> None:
+        super().__init__()
+        if mode not in MODES:
+            raise ValueError(f"unknown quantization mode {mode!r}; expected one of {MODES}")
+        if mode == "int8":
+            raise NotImplementedError("bnb.int8 (LLM.int8()) is specified in oracle/quant_ref.py but has no CUDA kernel yet")
+        if mode.endswith("-dq"):
+            raise NotImplementedError(f"{mode}: double quantisation of absmax is specified in oracle/quant_ref.py but "
+                                      "has no CUDA kernel yet; use the non-dq mode")
+        self.in_features, self.out_features = in_features, out_features
+        self.mode, self.compute_dtype = mode, compute_dtype
+        self.quant_type = mode.split("-")[0]  # nf4 | fp4 | int4
+        self.blocksize = 128 if self.quant_type == "int4" else 64
+        kw = dict(device=device, dtype=dtype)
+        self.weight = nn.Parameter(torch.empty((out_features, in_features), **kw), requires_grad=False)
+        self.bias = nn.Parameter(torch.empty(out_features, **kw), requires_grad=False) if bias else None
+        self.quant_state: Optional[List[Any]] = None
+        # int4 extras (canonical GPTQ-style tensors + the kernel-side interleaved {scale, zero})
+        self.scales: Optional[torch.Tensor] = None
+        self.qzeros: Optional[torch.Tensor] = None
+        self.sz: Optional[torch.Tensor] = None
+
+    # -- construction from an existing nn.Linear (convert_module path, generate/tp.py:171) -------------------
+    @classmethod
+    def from_linear(cls, linear: nn.Linear, mode: str, compute_dtype: torch.dtype) -> "QLinear":
+        q = cls(linear.in_features, linear.out_features, linear.bias is not None, device="meta", mode=mode,
+                compute_dtype=compute_dtype)
+        q.weight = nn.Parameter(linear.weight.data, requires_grad=False)
+        if linear.bias is not None:
+            q.bias = nn.Parameter(linear.bias.data, requires_grad=False)
+        if q.weight.is_cuda:
+            q.quantize_()
+        return q
+
+    @property
+    def is_quantized(self) -> bool:
+        return self.quant_state is not None
+
+    @property
+    def scale(self) -> torch.Tensor:
+        """The per-block scale tensor the kernels consume (fp32 absmax, or packed half2 {scale, zero} for int4)."""
+        return self.sz if self.quant_type == "int4" else self.quant_state[0]
+
+    @torch.no_grad()
+    def quantize_(self) -> None:
+        """Quantize the (CUDA, floating point) weight in place with the library's kernels."""
+        if self.is_quantized:
+            return
+        w = self.weight.data
+        if not w.is_cuda:
+            raise B200Error("QLinear quantizes on the GPU only (move the module to CUDA); there is no CPU path")
+        if w.dtype not in (torch.bfloat16, torch.float16, torch.float32):
+            raise B200Error(f"cannot quantize a weight of dtype {w.dtype}")
+        # the TP code edits in/out_features and assigns weight.data before the move (generate/tp.py:37-41)
+        shape = tuple(w.shape)
+        if shape != (self.out_features, self.in_features):
+            raise B200Error(f"weight shape {shape} does not match ({self.out_features}, {self.in_features})")
+        if self.quant_type == "int4":
+            qweight, scales, qzeros, sz = K.quantize_int4(w, self.blocksize)
+            self.scales, self.qzeros, self.sz = scales, qzeros, sz
+            self.weight = nn.Parameter(qweight, requires_grad=False)
+            self.quant_state = [scales, torch.Size(shape), w.dtype, self.blocksize, None, "int4", None]
+        else:
+            packed, absmax = K.quantize_4bit(w, self.quant_type, self.blocksize)
+            self.weight = nn.Parameter(packed, requires_grad=False)
+            self.quant_state = [absmax, torch.Size(shape), w.dtype, self.blocksize, None, self.quant_type, None]
+        if self.bias is not None and self.bias.dtype != self.compute_dtype:
+            self.bias = nn.Parameter(self.bias.data.to(self.compute_dtype), requires_grad=False)
+
+    def dequantize(self, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+        """(out_features, in_features) tensor of code[c] * absmax — bit-exact to oracle/quant_ref.py."""
+        if not self.is_quantized:
+            raise B200Error("QLinear is not quantized yet")
+        dtype = dtype or self.compute_dtype
+        shape = self.quant_state[1]
+        if self.quant_type == "int4":
+            return K.dequantize_int4(self.weight.data, self.scales, self.qzeros, shape[1], self.blocksize, dtype)
+        return K.dequantize_4bit(self.weight.data, self.quant_state[0], shape, dtype, self.quant_type, self.blocksize)
+
+    # -- device moves trigger quantization (bitsandbytes: Params4bit.cuda()) --------------------------------
+    def _apply(self, fn, recurse: bool = True):
+        if self.is_quantized:
+            # packed integer tensors must not be cast by .to(dtype); move everything by device only
+            probe = fn(torch.empty(0, dtype=torch.float32, device=self.weight.device))
+            dev = probe.device
+            if dev != self.weight.device:
+                if dev.type != "cuda":
+                    raise B200Error("a quantized QLinear cannot leave CUDA (no CPU path)")
+                self.weight = nn.Parameter(self.weight.data.to(dev), requires_grad=False)
+                self.quant_state[0] = self.quant_state[0].to(dev)
+                for name in ("scales", "qzeros", "sz"):
+                    t = getattr(self, name)
+                    if t is not None:
+                        setattr(self, name, t.to(dev))
+                if self.bias is not None:
+                    self.bias = nn.Parameter(self.bias.data.to(dev), requires_grad=False)
+            return self
+        super()._apply(fn, recurse)
+        if self.weight.is_cuda and self.weight.is_floating_point():
+            self.quantize_()
+        return self
+
+    # -- full-precision checkpoints load straight into a quantized module (lit_gpt/utils.py:354-356) ---------
+    def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys, error_msgs):
+        wkey, bkey = prefix + "weight", prefix + "bias"
+        if wkey in state_dict and state_dict[wkey].is_floating_point():
+            w = state_dict[wkey]
+            if tuple(w.shape) != (self.out_features, self.in_features):
+                error_msgs.append(f"size mismatch for {wkey}: checkpoint {tuple(w.shape)} vs module "
+                                  f"({self.out_features}, {self.in_features})")
+                return
+            target = self.weight.device
+            self.quant_state, self.scales, self.qzeros, self.sz = None, None, None, None
+            if target.type == "cuda":
+                self.weight = nn.Parameter(w.detach().to(target), requires_grad=False)
+                self.quantize_()
+            else:  # meta / cpu: keep the full-precision weight; quantization happens at the device move
+                self.weight = nn.Parameter(w.detach(), requires_grad=False)
+            if self.bias is not None:
+                if bkey in state_dict:
+                    b = state_dict[bkey].detach()
+                    self.bias = nn.Parameter(b.to(target) if target.type == "cuda" else b, requires_grad=False)
+                elif strict:
+                    missing_keys.append(bkey)
+            elif bkey in state_dict and strict:
+                unexpected_keys.append(bkey)
+            return
+        super()._load_from_state_dict(state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys, error_msgs)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if not self.is_quantized or not x.is_cuda:
+            raise B200Error("QLinear.forward needs the module quantized on CUDA and a CUDA input; there is no CPU "
+                            "fallback (move the model with fabric.setup_module / .to('cuda'))")
+        in_dtype = x.dtype
+        if in_dtype != torch.bfloat16:
+            x = x.to(torch.bfloat16)
+        rows = x.numel() // self.in_features
+        if rows <= GEMV_MAX_ROWS:
+            y = K.qgemv(x, self.weight.data, self.scale, self.out_features, self.in_features, self.quant_type,
+                        self.blocksize, bias=self.bias)
+        else:
+            y = prefill_linear(self, x)
+        return y if in_dtype == torch.bfloat16 else y.to(in_dtype)
+
+    def extra_repr(self) -> str:
+        return f"in_features={self.in_features}, out_features={self.out_features}, bias={self.bias is not None}, mode={self.mode}"
+
+
+def prefill_linear(q: QLinear, x: torch.Tensor) -> torch.Tensor:
+    """T > 16 rows: dense contraction.  Uses the library's prefill GEMM when it supports the shape; until the
+    tcgen05 kernel lands this is the reference's own formulation (dequantize_4bit to bf16, then a library GEMM,
+    SURVEY Q1) with the dequantisation done by this library's kernel."""
+    w = q.dequantize(torch.bfloat16)
+    return F.linear(x, w, q.bias)
+
+
+class QuantPrecision:
+    """Mirror of ``lightning.fabric.plugins.BitsandbytesPrecision(mode, dtype, ignore_modules)``."""
+
+    precision = "quantized"
+
+    def __init__(self, mode: str, dtype: Optional[torch.dtype] = None, ignore_modules: Optional[Set[str]] = None) -> None:
+        if mode.startswith(("bnb.", "gptq.")):
+            mode = mode.split(".", 1)[1]
+        if mode not in MODES:
+            raise ValueError(f"Unsupported quantization mode {mode!r}; supported: {MODES}")
+        self.mode = mode
+        self.dtype = dtype or torch.bfloat16
+        if self.dtype != torch.bfloat16:
+            raise NotImplementedError(f"b200gpt computes in bf16 (requested {self.dtype}); use --precision bf16-true")
+        self.ignore_modules = set(ignore_modules or ())
+
+    def convert_module(self, module: nn.Module) -> nn.Module:
+        n = _convert_layers(module, self.mode, self.dtype, self.ignore_modules)
+        if n == 0 and not any(isinstance(m, QLinear) for m in module.modules()):
+            raise TypeError("You are using the quantization plugin, but your model has no Linear layers.")
+        for m in module.modules():  # everything that is not a packed weight computes in `dtype`
+            for name, p in list(m.named_parameters(recurse=False)):
+                if p.is_floating_point() and p.dtype != self.dtype and not isinstance(m, QLinear):
+                    setattr(m, name, nn.Parameter(p.data.to(self.dtype), requires_grad=False))
+        return module
+
+    @contextlib.contextmanager
+    def tensor_init_context(self) -> Iterator[None]:
+        prev = torch.get_default_dtype()
+        torch.set_default_dtype(self.dtype)
+        try:
+            yield
+        finally:
+            torch.set_default_dtype(prev)
+
+    @contextlib.contextmanager
+    def module_init_context(self) -> Iterator[None]:
+        """Default dtype + ``torch.nn.Linear`` constructs QLinear (the reference's fabric.init_module path)."""
+        mode, dtype = self.mode, self.dtype
+        orig = torch.nn.Linear
+
+        class _Bound(QLinear):
+            def __init__(self, in_features, out_features, bias=True, device=None, dtype_=None, **kw):
+                super().__init__(in_features, out_features, bias, device=device, dtype=dtype_, mode=mode, compute_dtype=dtype)
+
+        with self.tensor_init_context():
+            torch.nn.Linear = _Bound  # type: ignore[misc]
+            try:
+                yield
+            finally:
+                torch.nn.Linear = orig  # type: ignore[misc]
+
+    forward_context = tensor_init_context
+
+
+def _convert_layers(module: nn.Module, mode: str, dtype: torch.dtype, ignore: Set[str], prefix: str = "") -> int:
+    n = 0
+    for name, child in module.named_children():
+        full = f"{prefix}.{name}" if prefix else name
+        if isinstance(child, nn.Linear) and not any(full.startswith(i) for i in ignore):
+            setattr(module, name, QLinear.from_linear(child, mode, dtype))
+            n += 1
+        else:
+            n += _convert_layers(child, mode, dtype, ignore, full)
+    return n
