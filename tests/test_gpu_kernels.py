@@ -1,0 +1,316 @@
+"""Parity of each CUDA kernel (through the C ABI) against the oracle, on seeded inputs.  Run with -m gpu on a B200."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_ref as M
+from oracle import quant_ref as Q
+from oracle import quant_ref_c as QC
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def K():
+    from lit_gpt_b200 import kernels
+
+    return kernels
+
+
+def _randw(shape, seed, dtype=torch.bfloat16, std=0.02):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(shape, generator=g) * std).to(dtype)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# quantise / dequantise: bit-exact
+# ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("qt", ["nf4", "fp4"])
+@pytest.mark.parametrize("shape,dtype", [((256, 512), torch.bfloat16), ((7, 33), torch.float32), ((1, 64), torch.float16),
+                                         ((3, 1), torch.bfloat16), ((4096, 1024), torch.bfloat16), ((64, 11008), torch.bfloat16)])
+def test_quantize_4bit_bit_exact(K, qt, shape, dtype):
+    w = _randw(shape, seed=sum(shape), dtype=dtype)
+    w[0, 0] = 0.0
+    packed, absmax = K.quantize_4bit(w.cuda(), qt)
+    p_ref, a_ref = QC.quantize_4bit(w.float().numpy(), qt)
+    assert packed.shape == p_ref.shape and packed.dtype == torch.uint8
+    assert np.array_equal(packed.cpu().numpy(), p_ref)
+    assert np.array_equal(absmax.cpu().numpy(), a_ref)
+    d32 = K.dequantize_4bit(packed, absmax, shape, torch.float32, qt)
+    d_ref = QC.dequantize_4bit(p_ref, a_ref, shape, qt)
+    assert np.array_equal(d32.cpu().numpy(), d_ref)
+    d16 = K.dequantize_4bit(packed, absmax, shape, torch.bfloat16, qt)
+    assert torch.equal(d16.cpu(), torch.from_numpy(d_ref).to(torch.bfloat16))
+    # idempotence through the device: quantise(dequantise) reproduces absmax and the dequantised values
+    p2, a2 = K.quantize_4bit(d32, qt)
+    assert torch.equal(a2, absmax) and torch.equal(K.dequantize_4bit(p2, a2, shape, torch.float32, qt), d32)
+
+
+def test_quantize_4bit_edge_blocks(K):
+    w = torch.zeros(3, 64)
+    w[1, 5], w[2, :] = 2.5, -1e-30  # all-zero block, single spike, denormal-scale block
+    packed, absmax = K.quantize_4bit(w.cuda(), "nf4")
+    p_ref, a_ref = Q.quantize_4bit(w.numpy(), "nf4")
+    assert np.array_equal(packed.cpu().numpy(), p_ref) and np.array_equal(absmax.cpu().numpy(), a_ref)
+    assert torch.all(K.dequantize_4bit(packed, absmax, (3, 64), torch.float32)[0] == 0)
+
+
+@pytest.mark.parametrize("shape", [(64, 256), (5, 200), (16, 4096), (3, 8), (32, 11008)])
+def test_int4_bit_exact(K, shape):
+    w = _randw(shape, seed=shape[1])
+    qw, scales, qz, sz = K.quantize_int4(w.cuda(), 128)
+    qw_ref, s_ref, z_ref = Q.quantize_int4_g128(w.float().numpy())
+    assert np.array_equal(qw.cpu().numpy().view(np.uint32), qw_ref)
+    assert np.array_equal(scales.cpu().numpy(), s_ref)
+    assert np.array_equal(qz.cpu().numpy().view(np.uint32), z_ref)
+    d = K.dequantize_int4(qw, scales, qz, shape[1], 128, torch.float32)
+    assert np.array_equal(d.cpu().numpy(), QC.dequantize_int4(qw_ref, s_ref, z_ref, shape[1]))
+    # kernel-side {scale, zero} pairs hold the same information
+    szn = sz.cpu().numpy().view(np.uint32)
+    assert np.array_equal((szn & 0xFFFF).astype(np.uint16).view(np.float16), s_ref)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# fused dequant-GEMV
+# ---------------------------------------------------------------------------------------------------------
+def _gemv_case(K, N, Kdim, B, qt, seed=0, **kw):
+    w = _randw((N, Kdim), seed)
+    x = _randw((B, Kdim), seed + 1, std=1.0)
+    wd = w.cuda()
+    if qt == "int4":
+        qw, scales, qz, sz = K.quantize_int4(wd, 128)
+        packed, scale, bs = qw, sz, 128
+        deq = QC.dequantize_int4(qw.cpu().numpy().view(np.uint32), scales.cpu().numpy(), qz.cpu().numpy().view(np.uint32), Kdim)
+    else:
+        packed, scale = K.quantize_4bit(wd, qt)
+        bs = 64
+        deq = QC.dequantize_4bit(packed.cpu().numpy(), scale.cpu().numpy(), (N, Kdim), qt)
+    return w, x, packed, scale, bs, torch.from_numpy(deq)
+
+
+def _check_gemv(y, x, deq, extra=None, post=None):
+    """kernel error against the wide oracle must stay within 2x the error of the plain bf16 torch composition."""
+    wide = x.double() @ deq.double().T
+    comp = torch.nn.functional.linear(x.cuda(), deq.to(torch.bfloat16).cuda()).float().cpu()  # reference's own formulation
+    if post is not None:
+        wide, comp = post(wide.float()).double(), post(comp)
+    e_k = (y.float().cpu().double() - wide).abs().max().item()
+    e_t = (comp.double() - wide).abs().max().item()
+    scale = wide.abs().max().item()
+    assert e_k <= 2.0 * e_t + 2 ** -8 * scale, f"kernel err {e_k:.4g} vs torch-bf16 err {e_t:.4g} (|y|max {scale:.3g})"
+
+
+@pytest.mark.parametrize("qt", ["nf4", "fp4", "int4"])
+@pytest.mark.parametrize("N,Kdim,B", [(512, 4096, 1), (4096, 4096, 1), (344, 11008, 1), (1000, 5120, 3), (4096, 1024, 8),
+                                      (2048, 4096, 16), (256, 256, 5), (20, 64, 1), (512, 8192, 2)])
+def test_qgemv_fast_path(K, qt, N, Kdim, B):
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, B, qt, seed=N + B)
+    y = K.qgemv(x.cuda(), packed, scale, N, Kdim, qt, bs)
+    assert y.shape == (B, N) and y.dtype == torch.bfloat16
+    _check_gemv(y, x.float(), deq)
+    y2 = K.qgemv(x.cuda(), packed, scale, N, Kdim, qt, bs)  # split-K counters are self-cleaning: run twice
+    assert torch.equal(y, y2), "not deterministic / workspace not clean between launches"
+
+
+@pytest.mark.parametrize("ks,occ", [(1, 1), (2, 2), (4, 1), (4, 3)])
+def test_qgemv_tuning_variants_agree(K, ks, occ):
+    w, x, packed, scale, bs, deq = _gemv_case(K, 1024, 4096, 2, "nf4", seed=5)
+    try:
+        K.qgemv_tune(ks, occ)
+        y = K.qgemv(x.cuda(), packed, scale, 1024, 4096, "nf4", bs)
+    finally:
+        K.qgemv_tune(0, 0)
+    _check_gemv(y, x.float(), deq)
+
+
+@pytest.mark.parametrize("qt", ["nf4", "int4"])
+@pytest.mark.parametrize("N,Kdim,B", [(86, 32, 1), (33, 100, 2), (352, 96, 16), (7, 8, 1)])
+def test_qgemv_generic_path_odd_shapes(K, qt, N, Kdim, B):
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, B, qt, seed=N)
+    y = K.qgemv(x.cuda(), packed, scale, N, Kdim, qt, bs)
+    _check_gemv(y, x.float(), deq)
+
+
+def test_qgemv_generic_equals_fast(K):
+    w, x, packed, scale, bs, deq = _gemv_case(K, 512, 1024, 4, "nf4", seed=9)
+    y_fast = K.qgemv(x.cuda(), packed, scale, 512, 1024, "nf4", bs)
+    try:
+        K.qgemv_tune(0, 0, force_generic=True)
+        y_gen = K.qgemv(x.cuda(), packed, scale, 512, 1024, "nf4", bs)
+    finally:
+        K.qgemv_tune(0, 0, False)
+    assert (y_fast.float() - y_gen.float()).abs().max() <= 2 ** -7 * y_gen.float().abs().max()
+
+
+@pytest.mark.parametrize("Kdim", [4096, 11008, 96])
+def test_qgemv_prologue_norm_and_residual_epilogue(K, Kdim):
+    N, B = 512, 2
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, B, "nf4", seed=Kdim)
+    nw = (1.0 + 0.1 * _randw((Kdim,), 3, std=1.0).float()).to(torch.bfloat16)
+    delta = _randw((B, Kdim), 4, std=0.5)
+    res = _randw((B, N), 5, std=1.0)
+    x_out = torch.empty(B, Kdim, dtype=torch.bfloat16, device="cuda")
+    y = K.qgemv(x.cuda(), packed, scale, N, Kdim, "nf4", bs, delta=delta.cuda(), x_out=x_out, norm_weight=nw.cuda(),
+                norm_eps=1e-5, residual=res.cuda())
+    xs = (x + delta)  # bf16 add, as `x = h + x` in the reference (model.py:591)
+    assert torch.equal(x_out.cpu(), xs)
+    xn = M.rmsnorm(xs, nw, 1e-5)  # oracle rounding points (rmsnorm.py:19-25)
+    h = (xn.double() @ deq.double().T).float().to(torch.bfloat16)
+    want = (h + res).float()
+    assert (y.float().cpu() - want).abs().max() <= 2 ** -6 * want.abs().max()
+
+
+@pytest.mark.parametrize("N,Kdim,B", [(11008, 4096, 1), (352, 256, 3), (1376, 4096, 8)])
+def test_qgemv_swiglu(K, N, Kdim, B):
+    w1, x, p1, s1, bs, d1 = _gemv_case(K, N, Kdim, B, "nf4", seed=1)
+    w2, _, p2, s2, _, d2 = _gemv_case(K, N, Kdim, B, "nf4", seed=2)
+    y = K.qgemv(x.cuda(), p1, s1, N, Kdim, "nf4", bs, packed2=p2, scale2=s2)
+    a = (x.double() @ d1.double().T).float().to(torch.bfloat16)
+    b = (x.double() @ d2.double().T).float().to(torch.bfloat16)
+    want = (torch.nn.functional.silu(a) * b).float()  # model.py:712-716 rounding points
+    assert (y.float().cpu() - want).abs().max() <= 2 ** -6 * want.abs().max() + 1e-6
+
+
+def test_qgemv_bias_and_errors(K):
+    from lit_gpt_b200._cabi import B200Error
+
+    w, x, packed, scale, bs, deq = _gemv_case(K, 256, 512, 1, "nf4", seed=3)
+    bias = _randw((256,), 7, std=1.0)
+    y = K.qgemv(x.cuda(), packed, scale, 256, 512, "nf4", bs, bias=bias.cuda())
+    want = (x.double() @ deq.double().T).float() + bias.float()
+    assert (y.float().cpu() - want).abs().max() <= 2 ** -6 * want.abs().max()
+    with pytest.raises(B200Error, match="batch"):
+        K.qgemv(torch.zeros(17, 512, dtype=torch.bfloat16, device="cuda"), packed, scale, 256, 512, "nf4", bs)
+    with pytest.raises(B200Error, match="bfloat16"):
+        K.qgemv(torch.zeros(1, 512, device="cuda"), packed, scale, 256, 512, "nf4", bs)
+    with pytest.raises(B200Error, match="CUDA"):
+        K.qgemv(torch.zeros(1, 512, dtype=torch.bfloat16), packed, scale, 256, 512, "nf4", bs)
+
+
+def test_qgemv_linearity_full_size(K):
+    """Size-independent property at the BASELINE shape (Llama-2-7B gate projection, 11008 x 4096):
+    y(a*x1 + x2) tracks a*y(x1) + y(x2), and a one-hot x reads back a dequantised weight column exactly."""
+    N, Kdim = 11008, 4096
+    w = _randw((N, Kdim), 11)
+    packed, absmax = K.quantize_4bit(w.cuda(), "nf4")
+    onehot = torch.zeros(1, Kdim, dtype=torch.bfloat16, device="cuda")
+    onehot[0, 1234] = 1.0
+    col = K.qgemv(onehot, packed, absmax, N, Kdim)
+    deq = K.dequantize_4bit(packed, absmax, (N, Kdim), torch.float32)
+    # the GEMV multiplies bf16(code) by absmax in fp32 and rounds once: within 1 bf16 ulp of the exact dequant value
+    assert (col[0].float() - deq[:, 1234]).abs().max() <= 2 ** -8 * deq[:, 1234].abs().max()
+    x1, x2 = _randw((1, Kdim), 1, std=1.0).cuda(), _randw((1, Kdim), 2, std=1.0).cuda()
+    lhs = K.qgemv((2 * x1 + x2), packed, absmax, N, Kdim).float()
+    rhs = 2 * K.qgemv(x1, packed, absmax, N, Kdim).float() + K.qgemv(x2, packed, absmax, N, Kdim).float()
+    assert (lhs - rhs).abs().max() <= 0.05 * rhs.abs().max()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# norm / embedding / argmax
+# ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("rows,dim", [(1, 4096), (5, 96), (16, 5120), (3, 8192)])
+def test_rmsnorm(K, rows, dim):
+    x, w = _randw((rows, dim), 1, std=1.0), (1 + _randw((dim,), 2, std=0.2).float()).to(torch.bfloat16)
+    y = K.rmsnorm(x.cuda(), w.cuda(), 1e-5)
+    want = M.rmsnorm(x, w, 1e-5)
+    assert (y.cpu().float() - want.float()).abs().max() <= 2 ** -7 * want.float().abs().max()
+    assert (y.cpu() == want).float().mean() > 0.99  # same rounding points: almost every element bit-equal
+    d = _randw((rows, dim), 3, std=1.0)
+    s = torch.empty_like(x).cuda()
+    y2 = K.rmsnorm(x.cuda(), w.cuda(), 1e-5, delta=d.cuda(), sum_out=s)
+    assert torch.equal(s.cpu(), x + d)
+    assert (y2.cpu().float() - M.rmsnorm(x + d, w, 1e-5).float()).abs().max() <= 2 ** -7 * 8
+
+
+def test_rmsnorm_golden_from_reference(K, golden):
+    u = golden("units")
+    x, w = torch.from_numpy(u["rms_x"]).bfloat16(), torch.from_numpy(u["rms_w"]).bfloat16()
+    y = K.rmsnorm(x.cuda(), w.cuda(), 1e-5).cpu().float()
+    ref = M.rmsnorm(x, w, 1e-5).float()
+    assert (y - ref).abs().max() <= 2 ** -7 * ref.abs().max()
+
+
+def test_embedding_and_argmax(K):
+    wte = _randw((1000, 256), 1, std=1.0).cuda()
+    idx = torch.tensor([[3], [999], [0]], device="cuda")
+    assert torch.equal(K.embedding(idx, wte), wte[idx])
+    logits = _randw((2, 32000), 5, std=1.0).cuda()
+    logits[0, 777] = 50.0
+    logits[0, 31999] = 50.0  # tie -> lowest index, as torch.argmax
+    tok = torch.zeros(2, dtype=torch.int64, device="cuda")
+    pos = torch.tensor([41], dtype=torch.int64, device="cuda")
+    hist = torch.zeros(64, dtype=torch.int64, device="cuda")
+    K.argmax_(logits, tok, pos_inout=pos, history=hist)
+    assert tok.tolist() == [777, int(torch.argmax(logits[1]))] and pos.item() == 42 and hist[42].item() == 777
+
+
+# ---------------------------------------------------------------------------------------------------------
+# fused rope + kv append + decode attention
+# ---------------------------------------------------------------------------------------------------------
+def _attn_oracle(qkv, cos, sin, pos, kc, vc, H, G, hs, n_elem):
+    """lit_gpt/model.py:624-665 restated with the oracle's ops on CPU (bf16 rope rounding, fp32 softmax)."""
+    B = qkv.shape[0]
+    qpk = H // G
+    t = qkv.view(B, 1, G, qpk + 2, hs).permute(0, 2, 3, 1, 4)
+    q, k, v = t.split((qpk, 1, 1), dim=2)
+    q = q.reshape(B, H, 1, hs)
+    k = k.reshape(B, G, 1, hs)
+    v = v.reshape(B, G, 1, hs)
+    c, s = cos[pos : pos + 1], sin[pos : pos + 1]
+    q = torch.cat((M.apply_rope(q[..., :n_elem], c, s), q[..., n_elem:]), -1)
+    k = torch.cat((M.apply_rope(k[..., :n_elem], c, s), k[..., n_elem:]), -1)
+    kc, vc = kc.clone(), vc.clone()
+    kc[:, :, pos] = k[:, :, 0]
+    vc[:, :, pos] = v[:, :, 0]
+    kk = kc[:, :, : pos + 1].float().repeat_interleave(qpk, dim=1)
+    vv = vc[:, :, : pos + 1].float().repeat_interleave(qpk, dim=1)
+    att = torch.softmax((q.float() @ kk.transpose(-1, -2)) / math.sqrt(hs), dim=-1)
+    y = (att @ vv).transpose(1, 2).reshape(B, H * hs)
+    return y, kc, vc
+
+
+@pytest.mark.parametrize("H,G,hs", [(32, 32, 128), (32, 8, 128), (8, 1, 128), (8, 8, 64), (4, 2, 64), (12, 4, 64), (16, 1, 64)])
+@pytest.mark.parametrize("pos,max_seq,B,splits", [(0, 64, 1, 0), (5, 64, 2, 1), (271, 272, 1, 0), (1000, 2048, 1, 7), (2047, 2048, 3, 0)])
+@pytest.mark.parametrize("table_dtype", [torch.float32, torch.bfloat16])
+def test_attn_decode(K, H, G, hs, pos, max_seq, B, splits, table_dtype):
+    if table_dtype == torch.bfloat16 and (pos not in (5, 1000) or hs != 128):
+        pytest.skip("bf16 tables: sampled subset")
+    g = torch.Generator().manual_seed(H * 1000 + pos)
+    n_elem = hs if H != 12 else hs // 4  # one partial-rotary case
+    qkv = torch.randn(B, (H + 2 * G) * hs, generator=g).bfloat16()
+    kc = torch.randn(B, G, max_seq, hs, generator=g).bfloat16()
+    vc = torch.randn(B, G, max_seq, hs, generator=g).bfloat16()
+    kc[:, :, pos:], vc[:, :, pos:] = 0, 0
+    cos, sin = M.build_rope_cache(max_seq, n_elem, pos_dtype=torch.float32)
+    cos, sin = cos.to(table_dtype), sin.to(table_dtype)
+    want, kc_ref, vc_ref = _attn_oracle(qkv, cos, sin, pos, kc, vc, H, G, hs, n_elem)
+    kcd, vcd = kc.cuda(), vc.cuda()
+    y = K.attn_decode(qkv.cuda(), cos.cuda(), sin.cuda(), torch.tensor([pos], device="cuda"), kcd, vcd, H, G, hs, n_elem,
+                      num_splits=splits)
+    assert torch.equal(kcd.cpu(), kc_ref) and torch.equal(vcd.cpu(), vc_ref), "cache append differs from the oracle"
+    assert (y.cpu().float() - want).abs().max() <= 2 ** -7 * max(1.0, want.abs().max().item())
+    # preselected table row (module path) gives the same answer
+    y2 = K.attn_decode(qkv.cuda(), cos[pos : pos + 1].cuda(), sin[pos : pos + 1].cuda(), torch.tensor([pos], device="cuda", dtype=torch.int32),
+                       kc.cuda(), vc.cuda(), H, G, hs, n_elem, num_splits=splits, table_preselected=True)
+    assert torch.equal(y, y2)
+
+
+def test_rope_kv_append(K):
+    B, T, H, G, hs, max_seq = 2, 9, 8, 2, 128, 32
+    g = torch.Generator().manual_seed(0)
+    qkv = torch.randn(B, T, (H + 2 * G) * hs, generator=g).bfloat16()
+    cos, sin = M.build_rope_cache(max_seq, hs, pos_dtype=torch.float32)
+    pos = torch.arange(3, 3 + T)
+    kc = torch.zeros(B, G, max_seq, hs, dtype=torch.bfloat16, device="cuda")
+    vc = torch.zeros_like(kc)
+    q = K.rope_kv_append(qkv.cuda(), cos.cuda(), sin.cuda(), pos.cuda(), kc, vc, H, G, hs, hs)
+    qpk = H // G
+    t = qkv.view(B, T, G, qpk + 2, hs).permute(0, 2, 3, 1, 4)
+    qq, kk, vv = t.split((qpk, 1, 1), dim=2)
+    q_ref = M.apply_rope(qq.reshape(B, H, T, hs), cos[pos], sin[pos])
+    k_ref = M.apply_rope(kk.reshape(B, G, T, hs), cos[pos], sin[pos])
+    assert torch.equal(q.cpu(), q_ref)
+    assert torch.equal(kc[:, :, 3 : 3 + T].cpu(), k_ref) and torch.equal(vc[:, :, 3 : 3 + T].cpu(), vv.reshape(B, G, T, hs))
+    assert kc[:, :, :3].abs().sum() == 0 and kc[:, :, 3 + T :].abs().sum() == 0
