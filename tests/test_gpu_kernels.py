@@ -93,7 +93,7 @@ def _gemv_case(K, N, Kdim, B, qt, seed=0, **kw):
 def _check_gemv(y, x, deq, extra=None, post=None):
     """kernel error against the wide oracle must stay within 2x the error of the plain bf16 torch composition."""
     wide = x.double() @ deq.double().T
-    comp = torch.nn.functional.linear(x.cuda(), deq.to(torch.bfloat16).cuda()).float().cpu()  # reference's own formulation
+    comp = torch.nn.functional.linear(x.to(torch.bfloat16).cuda(), deq.to(torch.bfloat16).cuda()).float().cpu()  # reference's own formulation
     if post is not None:
         wide, comp = post(wide.float()).double(), post(comp)
     e_k = (y.float().cpu().double() - wide).abs().max().item()
