@@ -97,6 +97,44 @@ typedef struct b200_qgemv_args {
 size_t b200_qgemv_workspace_bytes(void);
 int b200_qgemv(const b200_qgemv_args* args, b200_stream_t stream);
 
+/* ---- tiled weight layout + streaming GEMV (the decode hot path; csrc/tile.cu, csrc/qgemv_stream.cu) -----------
+ * b200_tile_4bit permutes the reference-layout arrays (packed + absmax of b200_quantize_4bit, or qweight + sz of
+ * b200_quantize_int4) into per-(16-row tile, 64-wide k-block) records laid out in warp-consumption order;
+ * b200_untile_4bit is the exact inverse (so the bitsandbytes-layout bytes are always recoverable bit for bit).
+ * K must be a multiple of 64 (NF4/FP4, blocksize 64) or 128 (INT4, group 128).  b200_tiled_bytes returns 0 for
+ * shapes the layout does not cover. */
+size_t b200_tiled_bytes(int64_t N, int64_t K, int qtype);
+int b200_tile_4bit(const void* packed, const void* scale, int64_t N, int64_t K, int qtype, int blocksize, void* tiled,
+                   b200_stream_t stream);
+int b200_untile_4bit(const void* tiled, int64_t N, int64_t K, int qtype, int blocksize, void* packed, void* scale,
+                     b200_stream_t stream);
+/* Same contract as b200_qgemv (prologue / epilogues / rounding points), reading tiled matrices; no workspace.
+ * `prefetch`/`prefetch_bytes` (optional): a range the kernel asks the L2 to fetch (cp.async.bulk.prefetch.L2) -
+ * the weights of the NEXT kernel in the decode graph - so HBM stays busy across the kernel boundary. */
+typedef struct b200_qgemv_tiled_args {
+  const void* tiled;
+  const void* tiled2;      /* second matrix for SWIGLU, else NULL */
+  int qtype;
+  int blocksize;           /* 64 for NF4/FP4, 128 for INT4 */
+  int64_t N, K;
+  const void* x;           /* (batch, K) bf16 */
+  const void* delta;       /* optional (batch, K) bf16 */
+  void* x_out;             /* optional (batch, K) bf16 */
+  const void* norm_weight; /* optional (K) bf16 */
+  float norm_eps;
+  int batch;
+  int epilogue;
+  const void* bias;        /* optional (N) bf16 */
+  const void* bias2;       /* optional (N) bf16, SWIGLU second matrix */
+  const void* residual;    /* (batch, N) bf16 for EPI_RESIDUAL; may alias y */
+  void* y;                 /* (batch, N) bf16 */
+  const void* prefetch;
+  int64_t prefetch_bytes;
+} b200_qgemv_tiled_args;
+int b200_qgemv_tiled(const b200_qgemv_tiled_args* args, b200_stream_t stream);
+/* tuning: depth in {0(auto),2,4,6} items loaded ahead per warp; ctas_per_sm in {0(auto),1,2}; l2_prefetch 0/1 */
+int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch);
+
 /* ---- RMSNorm (replaces lit_gpt/rmsnorm.py:19-25 and the residual add at lit_gpt/model.py:591) ------------
  * y = RMSNorm(x (+ delta)) * weight; if sum_out != NULL it receives bf16(x + delta).  rows x dim, bf16. */
 int b200_rmsnorm(const void* x, const void* delta, const void* weight, float eps, void* y, void* sum_out,

@@ -30,6 +30,16 @@ class QGemvArgs(ctypes.Structure):
     ]
 
 
+class QGemvTiledArgs(ctypes.Structure):
+    _fields_ = [
+        ("tiled", c_void_p), ("tiled2", c_void_p), ("qtype", c_int), ("blocksize", c_int), ("N", c_int64), ("K", c_int64),
+        ("x", c_void_p), ("delta", c_void_p), ("x_out", c_void_p), ("norm_weight", c_void_p),
+        ("norm_eps", c_float), ("batch", c_int), ("epilogue", c_int),
+        ("bias", c_void_p), ("bias2", c_void_p), ("residual", c_void_p), ("y", c_void_p),
+        ("prefetch", c_void_p), ("prefetch_bytes", c_int64),
+    ]
+
+
 class AttnDecodeArgs(ctypes.Structure):
     _fields_ = [
         ("qkv", c_void_p), ("cos", c_void_p), ("sin", c_void_p), ("table_dtype", c_int), ("table_preselected", c_int), ("rope_n_elem", c_int),
@@ -60,6 +70,11 @@ _SIGNATURES = {
     "b200_dequantize_int4": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_int, c_void_p]),
     "b200_qgemv_workspace_bytes": (c_size_t, []),
     "b200_qgemv": (c_int, [ctypes.POINTER(QGemvArgs), c_void_p]),
+    "b200_tiled_bytes": (c_size_t, [c_int64, c_int64, c_int]),
+    "b200_tile_4bit": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p]),
+    "b200_untile_4bit": (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "b200_qgemv_tiled": (c_int, [ctypes.POINTER(QGemvTiledArgs), c_void_p]),
+    "b200_qgemv_tiled_tune": (c_int, [c_int, c_int, c_int]),
     "b200_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
     "b200_attn_decode_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_attn_decode": (c_int, [ctypes.POINTER(AttnDecodeArgs), c_void_p]),

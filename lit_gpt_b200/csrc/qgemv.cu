@@ -482,7 +482,7 @@ int b200_qgemv(const b200_qgemv_args* a, b200_stream_t stream) {
   const bool aligned = ((reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(a->packed) |
                          reinterpret_cast<uintptr_t>(a->delta) | reinterpret_cast<uintptr_t>(a->x_out) |
                          reinterpret_cast<uintptr_t>(a->norm_weight) | reinterpret_cast<uintptr_t>(a->packed2)) & 15) == 0;
-  const bool fast_fmt = (a->qtype == B200_Q_INT4) ? true : (a->blocksize == 64);
+  const bool fast_fmt = (a->qtype == B200_Q_INT4) ? (a->K % a->blocksize == 0) : (a->blocksize == 64);
   const bool fast = fast_fmt && (a->K % 64 == 0) && aligned && !g_tune_generic.load() && a->N >= 8 &&
                     (a->epilogue != B200_EPI_SWIGLU || a->bias == nullptr);
 

@@ -118,6 +118,71 @@ def qgemv(x: torch.Tensor, packed: torch.Tensor, scale: torch.Tensor, N: int, K:
 
 
 # ---------------------------------------------------------------------------------------------------------
+# tiled layout + streaming GEMV (the decode hot path)
+# ---------------------------------------------------------------------------------------------------------
+def tiled_bytes(N: int, K: int, quant_type: str = "nf4") -> int:
+    """Size of the tiled buffer for an (N, K) matrix; 0 when the layout does not cover the shape."""
+    return int(C.load().b200_tiled_bytes(N, K, QTYPES[quant_type]))
+
+
+def tile_4bit(packed: torch.Tensor, scale: torch.Tensor, N: int, K: int, quant_type: str = "nf4", blocksize: int = 64,
+              out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Reference-layout (packed, absmax) or (qweight, sz) -> flat uint8 tiled buffer (csrc/tile.cu)."""
+    C.require_cuda(packed, scale)
+    nbytes = tiled_bytes(N, K, quant_type)
+    if nbytes == 0:
+        raise C.B200Error(f"tile_4bit: shape ({N}, {K}) is not covered by the tiled layout for {quant_type}")
+    if out is None:
+        out = torch.empty(nbytes, dtype=torch.uint8, device=packed.device)
+    C.check(C.load().b200_tile_4bit(packed.data_ptr(), scale.data_ptr(), N, K, QTYPES[quant_type], blocksize, out.data_ptr(),
+                                    C.stream_ptr(packed.device)), "tile_4bit")
+    return out
+
+
+def untile_4bit(tiled: torch.Tensor, N: int, K: int, quant_type: str = "nf4", blocksize: int = 64):
+    """Inverse of tile_4bit -> (packed, scale) in the reference layout, bit for bit."""
+    C.require_cuda(tiled)
+    if quant_type == "int4":
+        packed = torch.empty((N, K // 8), dtype=torch.int32, device=tiled.device)
+        scale = torch.empty((N, K // blocksize), dtype=torch.int32, device=tiled.device)
+    else:
+        packed = torch.empty((N * K // 2, 1), dtype=torch.uint8, device=tiled.device)
+        scale = torch.empty((N * K // blocksize,), dtype=torch.float32, device=tiled.device)
+    C.check(C.load().b200_untile_4bit(tiled.data_ptr(), N, K, QTYPES[quant_type], blocksize, packed.data_ptr(), scale.data_ptr(),
+                                      C.stream_ptr(tiled.device)), "untile_4bit")
+    return packed, scale
+
+
+def qgemv_tiled(x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, quant_type: str = "nf4", blocksize: int = 64, *,
+                bias: Optional[torch.Tensor] = None, bias2: Optional[torch.Tensor] = None, delta: Optional[torch.Tensor] = None,
+                x_out: Optional[torch.Tensor] = None, norm_weight: Optional[torch.Tensor] = None, norm_eps: float = 1e-5,
+                residual: Optional[torch.Tensor] = None, tiled2: Optional[torch.Tensor] = None,
+                prefetch: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = epilogue(prologue(x) @ dequant(W).T) over tiled matrices; see b200_qgemv_tiled in include/b200gpt.h."""
+    C.require_cuda(x, tiled)
+    x = _bf16c(x, "x")
+    if x.shape[-1] != K:
+        raise C.B200Error(f"qgemv_tiled: x has {x.shape[-1]} features, weight expects {K}")
+    lead = x.shape[:-1]
+    batch = x.numel() // K
+    epilogue = C.EPI_SWIGLU if tiled2 is not None else (C.EPI_RESIDUAL if residual is not None else C.EPI_STORE)
+    y = out if out is not None else torch.empty((*lead, N), dtype=torch.bfloat16, device=x.device)
+    delta, residual, bias, bias2, norm_weight = (_bf16c(delta, "delta"), _bf16c(residual, "residual"), _bf16c(bias, "bias"),
+                                                 _bf16c(bias2, "bias2"), _bf16c(norm_weight, "norm_weight"))
+    args = C.QGemvTiledArgs(
+        tiled=tiled.data_ptr(), tiled2=C.ptr(tiled2), qtype=QTYPES[quant_type], blocksize=blocksize, N=N, K=K, x=x.data_ptr(),
+        delta=C.ptr(delta), x_out=C.ptr(x_out), norm_weight=C.ptr(norm_weight), norm_eps=norm_eps, batch=batch, epilogue=epilogue,
+        bias=C.ptr(bias), bias2=C.ptr(bias2), residual=C.ptr(residual), y=y.data_ptr(), prefetch=C.ptr(prefetch),
+        prefetch_bytes=0 if prefetch is None else prefetch.numel() * prefetch.element_size())
+    C.check(C.load().b200_qgemv_tiled(ctypes.byref(args), C.stream_ptr(x.device)), "qgemv_tiled")
+    return y
+
+
+def qgemv_tiled_tune(depth: int = 0, ctas_per_sm: int = 0, l2_prefetch: bool = True) -> None:
+    C.load().b200_qgemv_tiled_tune(depth, ctas_per_sm, int(l2_prefetch))
+
+
+# ---------------------------------------------------------------------------------------------------------
 # norm / embedding / argmax
 # ---------------------------------------------------------------------------------------------------------
 def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float = 1e-5, delta: Optional[torch.Tensor] = None,

@@ -192,32 +192,34 @@ class GPT(nn.Module):
         delta: Optional[torch.Tensor] = None
         eps = c.norm_eps
 
-        def lin(q: QLinear, inp: torch.Tensor, **kw: Any) -> torch.Tensor:
-            return K.qgemv(inp, q.weight.data, q.scale, q.out_features, q.in_features, q.quant_type, q.blocksize, **kw)
+        def lin(q: QLinear, inp: torch.Tensor, nxt: Optional[QLinear] = None, **kw: Any) -> torch.Tensor:
+            # nxt: the Linear of the NEXT GEMV in the step; its tiled weights are prefetched into L2 by this kernel
+            return q.gemv(inp, prefetch=None if nxt is None else nxt.tiled, **kw)
 
-        for block in self.transformer.h:
+        blocks = list(self.transformer.h)
+        for li, block in enumerate(blocks):
             a, m, cache = block.attn, block.mlp, block.attn.kv_cache
+            nxt_qkv = blocks[li + 1].attn.attn if li + 1 < len(blocks) else self.lm_head
             if delta is not None:  # TP: the all-reduced branch output is added in the next prologue
                 x_new = torch.empty_like(x)
-                qkv = lin(a.attn, x, delta=delta, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps)
+                qkv = lin(a.attn, x, a.proj, delta=delta, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps)
                 x = x_new
             else:
-                qkv = lin(a.attn, x, norm_weight=block.norm_1.weight, norm_eps=eps)
+                qkv = lin(a.attn, x, a.proj, norm_weight=block.norm_1.weight, norm_eps=eps)
             y = K.attn_decode(qkv, self.cos, self.sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups,
                               c.head_size, c.rope_n_elem)
             if tp:
-                h = self._all_reduce(lin(a.proj, y))
+                h = self._all_reduce(lin(a.proj, y, m.fc_1))
                 x_new = torch.empty_like(x)
-                act = lin(m.fc_1, x, delta=h, x_out=x_new, norm_weight=block.norm_2.weight, norm_eps=eps,
-                          packed2=m.fc_2.weight.data, scale2=m.fc_2.scale)
+                act = lin(m.fc_1, x, m.proj, other=m.fc_2, delta=h, x_out=x_new, norm_weight=block.norm_2.weight, norm_eps=eps)
                 x = x_new
-                delta = self._all_reduce(lin(m.proj, act))
+                delta = self._all_reduce(lin(m.proj, act, nxt_qkv))
             else:
-                x = lin(a.proj, y, residual=x)
-                act = lin(m.fc_1, x, norm_weight=block.norm_2.weight, norm_eps=eps, packed2=m.fc_2.weight.data,
-                          scale2=m.fc_2.scale)
-                x = lin(m.proj, act, residual=x)
-        logits = lin(self.lm_head, x, delta=delta, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+                x = lin(a.proj, y, m.fc_1, residual=x)
+                act = lin(m.fc_1, x, m.proj, other=m.fc_2, norm_weight=block.norm_2.weight, norm_eps=eps)
+                x = lin(m.proj, act, nxt_qkv, residual=x)
+        first = blocks[0].attn.attn if blocks else None  # graph replays run back to back: wrap the prefetch around
+        logits = lin(self.lm_head, x, first, delta=delta, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
         return logits.view(B, 1, -1)
 
 
@@ -361,9 +363,7 @@ class LLaMAMLP(nn.Module):
                 and x.dtype == torch.bfloat16 and rows <= 16 and f1.bias is None and f2.bias is None
                 and f1.quant_type == f2.quant_type):
             # gate and up projections + SwiGLU in one pass over both weight matrices
-            act = K.qgemv(x, f1.weight.data, f1.scale, f1.out_features, f1.in_features, f1.quant_type, f1.blocksize,
-                          packed2=f2.weight.data, scale2=f2.scale)
-            return self.proj(act)
+            return self.proj(f1.gemv(x, other=f2))
         x_fc_1 = self.fc_1(x)
         x_fc_2 = self.fc_2(x)
         x = F.silu(x_fc_1) * x_fc_2

@@ -55,6 +55,8 @@ class QLinear(nn.Module):
         self.scales: Optional[torch.Tensor] = None
         self.qzeros: Optional[torch.Tensor] = None
         self.sz: Optional[torch.Tensor] = None
+        # kernel-side tiled copy (csrc/tile.cu) consumed by the streaming GEMV; None when the shape is not covered
+        self.tiled: Optional[torch.Tensor] = None
 
     # -- construction from an existing nn.Linear (convert_module path, generate/tp.py:171) -------------------
     @classmethod
@@ -102,6 +104,9 @@ class QLinear(nn.Module):
             self.quant_state = [absmax, torch.Size(shape), w.dtype, self.blocksize, None, self.quant_type, None]
         if self.bias is not None and self.bias.dtype != self.compute_dtype:
             self.bias = nn.Parameter(self.bias.data.to(self.compute_dtype), requires_grad=False)
+        self.tiled = None
+        if K.tiled_bytes(shape[0], shape[1], self.quant_type):
+            self.tiled = K.tile_4bit(self.weight.data, self.scale, shape[0], shape[1], self.quant_type, self.blocksize)
 
     def dequantize(self, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
         """(out_features, in_features) tensor of code[c] * absmax — bit-exact to oracle/quant_ref.py."""
@@ -124,7 +129,7 @@ class QLinear(nn.Module):
                     raise B200Error("a quantized QLinear cannot leave CUDA (no CPU path)")
                 self.weight = nn.Parameter(self.weight.data.to(dev), requires_grad=False)
                 self.quant_state[0] = self.quant_state[0].to(dev)
-                for name in ("scales", "qzeros", "sz"):
+                for name in ("scales", "qzeros", "sz", "tiled"):
                     t = getattr(self, name)
                     if t is not None:
                         setattr(self, name, t.to(dev))
@@ -146,7 +151,7 @@ class QLinear(nn.Module):
                                   f"({self.out_features}, {self.in_features})")
                 return
             target = self.weight.device
-            self.quant_state, self.scales, self.qzeros, self.sz = None, None, None, None
+            self.quant_state, self.scales, self.qzeros, self.sz, self.tiled = None, None, None, None, None
             if target.type == "cuda":
                 self.weight = nn.Parameter(w.detach().to(target), requires_grad=False)
                 self.quantize_()
@@ -172,11 +177,25 @@ class QLinear(nn.Module):
             x = x.to(torch.bfloat16)
         rows = x.numel() // self.in_features
         if rows <= GEMV_MAX_ROWS:
-            y = K.qgemv(x, self.weight.data, self.scale, self.out_features, self.in_features, self.quant_type,
-                        self.blocksize, bias=self.bias)
+            y = self.gemv(x, bias=self.bias)
         else:
             y = prefill_linear(self, x)
         return y if in_dtype == torch.bfloat16 else y.to(in_dtype)
+
+    def gemv(self, x: torch.Tensor, other: Optional["QLinear"] = None, prefetch: Optional[torch.Tensor] = None,
+             **kw: Any) -> torch.Tensor:
+        """<= 16 activation rows through the fused dequant-GEMV: the streaming kernel over the tiled layout when the
+        shape is covered (and the activation fits its shared memory), else the reference-layout kernel.
+        ``other``: the up-projection for the fused SwiGLU pair (this module being the gate)."""
+        rows = x.numel() // self.in_features
+        if self.tiled is not None and (other is None or other.tiled is not None) and rows * (2 * self.in_features + 16) <= 96 * 1024:
+            return K.qgemv_tiled(x, self.tiled, self.out_features, self.in_features, self.quant_type, self.blocksize,
+                                 tiled2=None if other is None else other.tiled, prefetch=prefetch, **kw)
+        if other is not None:
+            kw.update(packed2=other.weight.data, scale2=other.scale)
+        kw.pop("bias2", None)
+        return K.qgemv(x, self.weight.data, self.scale, self.out_features, self.in_features, self.quant_type,
+                       self.blocksize, **kw)
 
     def extra_repr(self) -> str:
         return f"in_features={self.in_features}, out_features={self.out_features}, bias={self.bias is not None}, mode={self.mode}"

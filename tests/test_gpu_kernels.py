@@ -314,3 +314,106 @@ def test_rope_kv_append(K):
     assert torch.equal(q.cpu(), q_ref)
     assert torch.equal(kc[:, :, 3 : 3 + T].cpu(), k_ref) and torch.equal(vc[:, :, 3 : 3 + T].cpu(), vv.reshape(B, G, T, hs))
     assert kc[:, :, :3].abs().sum() == 0 and kc[:, :, 3 + T :].abs().sum() == 0
+
+
+# ---------------------------------------------------------------------------------------------------------
+# tiled layout + streaming GEMV (the decode hot path)
+# ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("qt", ["nf4", "fp4", "int4"])
+@pytest.mark.parametrize("N,Kdim", [(512, 4096), (344, 11008), (1000, 5120), (20, 128), (7, 256), (4096, 1024)])
+def test_tile_untile_roundtrip_bit_exact(K, qt, N, Kdim):
+    """The tiled layout is a pure permutation of the reference bytes: untile(tile(.)) is the identity, bit for bit."""
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, 1, qt, seed=N)
+    tiled = K.tile_4bit(packed, scale, N, Kdim, qt, bs)
+    assert tiled.numel() == K.tiled_bytes(N, Kdim, qt) > 0
+    p2, s2 = K.untile_4bit(tiled, N, Kdim, qt, bs)
+    assert torch.equal(p2.view(torch.uint8).flatten(), packed.view(torch.uint8).flatten())
+    assert torch.equal(s2.view(torch.uint8).flatten(), scale.view(torch.uint8).flatten())
+
+
+def test_tiled_layout_unsupported_shapes(K):
+    assert K.tiled_bytes(64, 96, "nf4") == 0 and K.tiled_bytes(64, 64, "int4") == 0 and K.tiled_bytes(64, 64, "nf4") > 0
+
+
+@pytest.mark.parametrize("qt", ["nf4", "fp4", "int4"])
+@pytest.mark.parametrize("N,Kdim,B", [(512, 4096, 1), (4096, 4096, 1), (344, 11008, 1), (1000, 5120, 3), (4096, 1024, 8),
+                                      (2048, 4096, 9), (256, 256, 5), (20, 128, 1), (512, 8192, 2), (12288, 4096, 1), (40, 1024, 16)])
+@pytest.mark.parametrize("depth", [0, 2, 6])
+def test_qgemv_tiled(K, qt, N, Kdim, B, depth):
+    if depth and (N, Kdim, B) not in ((512, 4096, 1), (344, 11008, 1), (1000, 5120, 3)):
+        pytest.skip("depth variants: sampled subset")
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, B, qt, seed=N + B)
+    tiled = K.tile_4bit(packed, scale, N, Kdim, qt, bs)
+    try:
+        K.qgemv_tiled_tune(depth, 0, True)
+        y = K.qgemv_tiled(x.cuda(), tiled, N, Kdim, qt, bs, prefetch=tiled)
+        y2 = K.qgemv_tiled(x.cuda(), tiled, N, Kdim, qt, bs)
+    finally:
+        K.qgemv_tiled_tune(0, 0, True)
+    assert y.shape == (B, N) and y.dtype == torch.bfloat16
+    _check_gemv(y, x.float(), deq)
+    assert torch.equal(y, y2), "not deterministic"
+    y_ref = K.qgemv(x.cuda(), packed, scale, N, Kdim, qt, bs)  # reference-layout kernel: same arithmetic, other k order
+    assert (y.float() - y_ref.float()).abs().max() <= 2 ** -6 * max(1e-3, y_ref.float().abs().max().item())
+
+
+@pytest.mark.parametrize("qt", ["nf4", "int4"])
+@pytest.mark.parametrize("Kdim", [4096, 11008, 128])
+def test_qgemv_tiled_prologue_norm_and_residual_epilogue(K, qt, Kdim):
+    N, B = 520, 2
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, B, qt, seed=Kdim)
+    tiled = K.tile_4bit(packed, scale, N, Kdim, qt, bs)
+    nw = (1.0 + 0.1 * _randw((Kdim,), 3, std=1.0).float()).to(torch.bfloat16)
+    delta = _randw((B, Kdim), 4, std=0.5)
+    res = _randw((B, N), 5, std=1.0)
+    x_out = torch.empty(B, Kdim, dtype=torch.bfloat16, device="cuda")
+    y = K.qgemv_tiled(x.cuda(), tiled, N, Kdim, qt, bs, delta=delta.cuda(), x_out=x_out, norm_weight=nw.cuda(), norm_eps=1e-5,
+                      residual=res.cuda())
+    xs = (x + delta)  # bf16 add, as `x = h + x` in the reference (model.py:591)
+    assert torch.equal(x_out.cpu(), xs)
+    xn = M.rmsnorm(xs, nw, 1e-5)  # oracle rounding points (rmsnorm.py:19-25)
+    h = (xn.double() @ deq.double().T).float().to(torch.bfloat16)
+    want = (h + res).float()
+    assert (y.float().cpu() - want).abs().max() <= 2 ** -6 * want.abs().max()
+
+
+@pytest.mark.parametrize("qt", ["nf4", "int4"])
+@pytest.mark.parametrize("N,Kdim,B", [(11008, 4096, 1), (352, 256, 3), (1376, 4096, 8), (1000, 1024, 12)])
+def test_qgemv_tiled_swiglu(K, qt, N, Kdim, B):
+    w1, x, p1, s1, bs, d1 = _gemv_case(K, N, Kdim, B, qt, seed=1)
+    w2, _, p2, s2, _, d2 = _gemv_case(K, N, Kdim, B, qt, seed=2)
+    t1, t2 = K.tile_4bit(p1, s1, N, Kdim, qt, bs), K.tile_4bit(p2, s2, N, Kdim, qt, bs)
+    y = K.qgemv_tiled(x.cuda(), t1, N, Kdim, qt, bs, tiled2=t2)
+    a = (x.double() @ d1.double().T).float().to(torch.bfloat16)
+    b = (x.double() @ d2.double().T).float().to(torch.bfloat16)
+    want = (torch.nn.functional.silu(a) * b).float()  # model.py:712-716 rounding points
+    assert (y.float().cpu() - want).abs().max() <= 2 ** -6 * want.abs().max() + 1e-6
+
+
+def test_qgemv_tiled_bias_and_errors(K):
+    from lit_gpt_b200._cabi import B200Error
+
+    w, x, packed, scale, bs, deq = _gemv_case(K, 256, 512, 1, "nf4", seed=3)
+    tiled = K.tile_4bit(packed, scale, 256, 512, "nf4", bs)
+    bias = _randw((256,), 7, std=1.0)
+    y = K.qgemv_tiled(x.cuda(), tiled, 256, 512, "nf4", bs, bias=bias.cuda())
+    want = (x.double() @ deq.double().T).float() + bias.float()
+    assert (y.float().cpu() - want).abs().max() <= 2 ** -6 * want.abs().max()
+    with pytest.raises(B200Error, match="batch"):
+        K.qgemv_tiled(torch.zeros(17, 512, dtype=torch.bfloat16, device="cuda"), tiled, 256, 512, "nf4", bs)
+    with pytest.raises(NotImplementedError, match="shared memory"):
+        K.qgemv_tiled(torch.zeros(16, 8192, dtype=torch.bfloat16, device="cuda"),
+                      torch.zeros(K.tiled_bytes(16, 8192, "nf4"), dtype=torch.uint8, device="cuda"), 16, 8192, "nf4", bs)
+
+
+def test_qgemv_tiled_onehot_reads_dequantised_column(K):
+    """Size-independent property at the BASELINE shape (Llama-2-7B gate projection 11008 x 4096)."""
+    N, Kdim = 11008, 4096
+    w = _randw((N, Kdim), 11)
+    packed, absmax = K.quantize_4bit(w.cuda(), "nf4")
+    tiled = K.tile_4bit(packed, absmax, N, Kdim)
+    onehot = torch.zeros(1, Kdim, dtype=torch.bfloat16, device="cuda")
+    onehot[0, 1234] = 1.0
+    col = K.qgemv_tiled(onehot, tiled, N, Kdim)
+    deq = K.dequantize_4bit(packed, absmax, (N, Kdim), torch.float32)
+    assert (col[0].float() - deq[:, 1234]).abs().max() <= 2 ** -8 * deq[:, 1234].abs().max()

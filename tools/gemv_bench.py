@@ -31,6 +31,9 @@ def main() -> None:
     ap.add_argument("--reps", type=int, default=30)
     ap.add_argument("--pdl", type=int, default=1)
     ap.add_argument("--json", action="store_true")
+    ap.add_argument("--kernel", choices=["tiled", "ref"], default="tiled")
+    ap.add_argument("--depth", type=int, default=0)
+    ap.add_argument("--l2pf", type=int, default=1)
     args = ap.parse_args()
 
     from lit_gpt_b200 import Config
@@ -44,6 +47,8 @@ def main() -> None:
     dev = torch.device("cuda")
     K.set_pdl(bool(args.pdl))
     K.qgemv_tune(args.ks, args.occ)
+    K.qgemv_tiled_tune(args.depth, args.occ, bool(args.l2pf))
+    tiled = args.kernel == "tiled"
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
     rows = []
     for name, N, Kd, kind in shapes:
@@ -55,10 +60,10 @@ def main() -> None:
             w = torch.empty(N, Kd, dtype=torch.bfloat16, device=dev).normal_(0, 0.02)
             if args.qt == "int4":
                 qw, _, _, sz = K.quantize_int4(w, 128)
-                mats.append((qw, sz, 128))
+                mats.append((K.tile_4bit(qw, sz, N, Kd, "int4", 128), None, 128) if tiled else (qw, sz, 128))
             else:
                 p, a = K.quantize_4bit(w, args.qt)
-                mats.append((p, a, 64))
+                mats.append((K.tile_4bit(p, a, N, Kd, args.qt, 64), None, 64) if tiled else (p, a, 64))
             del w
         x = torch.randn(args.batch, Kd, device=dev).to(torch.bfloat16)
         nw = torch.ones(Kd, dtype=torch.bfloat16, device=dev)
@@ -72,6 +77,12 @@ def main() -> None:
                 kw.update(norm_weight=nw, norm_eps=1e-5)
             if kind == "res":
                 kw.update(residual=res)
+            if tiled:
+                if kind == "swiglu":
+                    kw.update(tiled2=mats[i * nmat + 1][0])
+                nxt = mats[((i + 1) % copies) * nmat][0] if args.l2pf else None  # the chain's next launch reads these
+                K.qgemv_tiled(x, p, N, Kd, args.qt, bs, out=y, prefetch=nxt, **kw)
+                return
             if kind == "swiglu":
                 kw.update(packed2=mats[i * nmat + 1][0], scale2=mats[i * nmat + 1][1])
             K.qgemv(x, p, s, N, Kd, args.qt, bs, out=y, **kw)
@@ -117,7 +128,7 @@ def main() -> None:
         del mats
         torch.cuda.empty_cache()
     per_layer = sum(r["chain_us"] for r in rows[:4])
-    summary = {"model": args.model, "qt": args.qt, "batch": args.batch, "ks": args.ks, "occ": args.occ, "pdl": args.pdl,
+    summary = {"model": args.model, "qt": args.qt, "batch": args.batch, "kernel": args.kernel, "depth": args.depth, "l2pf": args.l2pf, "ks": args.ks, "occ": args.occ, "pdl": args.pdl,
                "per_layer_us": round(per_layer, 2), "step_est_us": round(per_layer * c.n_layer + rows[4]["chain_us"], 1), "rows": rows}
     print(json.dumps(summary), flush=True)
 
