@@ -41,6 +41,7 @@ struct StreamParams {
   const __nv_bfloat16* residual;
   __nv_bfloat16* y;
   int xstride;         // shared-memory row stride of the activation, in bf16 elements (K + 8)
+  int stages;          // ring stages per warp (2..4)
   const uint8_t* pf;   // L2 prefetch range (next kernel's weights), may be null
   int64_t pf_bytes;
 };
@@ -78,81 +79,104 @@ __device__ __forceinline__ void prefetch_l2_bulk(const void* p, uint32_t bytes) 
 
 __device__ __forceinline__ float silu_bf16_s(float a) { return round_bf16(a / (1.0f + expf(-a))); }
 
-struct SItem {
-  uint4 w0, w1;  // 16 B of tile 0 / tile 1: {row g bytes 0..7, row g+8 bytes 0..7}
-  uint2 s0, s1;  // scale words of rows g, g+8 for tile 0 / tile 1
-};
+// ---- mbarrier / bulk-copy (TMA) helpers ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint64_t pol) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol) : "memory");
+}
 
-// NB: batch column groups of 8 (batch <= 8*NB); INT4: int4 group-128 records; D: load-ahead depth in items.
-template <int NB, bool INT4, int D>
-__global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const StreamParams p) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
+constexpr int kGroups = 2;                      // row groups per CTA (each: 8 warps splitting K for one pair)
+constexpr int kSThreadsAll = kGroups * kSThreads;
+constexpr int kChunkBlocks = 2;                 // k-blocks per ring stage (per tile)
+constexpr int kMaxStages = 4;
+
+// Shared-memory layout (dynamic): [LUT 64 KB][mbarriers][red: groups x 8 warps x 2 tiles x 16 x COLS][ssq][rstd][xsum]
+// [x rows][ring: 16 warps x stages x stage_bytes].
+template <int NB, bool INT4>
+__global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const StreamParams p) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
   constexpr int COLS = 8 * NB;
-  constexpr int RED_ONE = kSWarps * 2 * 16 * COLS;  // floats per reduction buffer
+  constexpr int RED_GROUP = kSWarps * 2 * 16 * COLS;       // floats per group
+  constexpr int C = kChunkBlocks;
+  constexpr int BLK_BYTES = INT4 ? 544 : 576;              // bytes per k-block per tile inside a record stream
+  constexpr int STAGE_TILE = C * BLK_BYTES;                // one tile's part of a stage
+  constexpr int STAGE = 2 * STAGE_TILE;                    // two tiles
   uint32_t* lut = reinterpret_cast<uint32_t*>(smem_raw);
-  float* red = reinterpret_cast<float*>(smem_raw + kSLutBytes);                 // [2][8 warps][2 tiles][16][COLS]
-  float* s_ssq = red + 2 * RED_ONE;                                             // [8 warps][16]
-  float* s_rstd = s_ssq + kSWarps * 16;                                         // [16]
-  float* xsum_s = s_rstd + 16;                                                  // INT4: [batch][nkb]
-  __nv_bfloat16* x_s = reinterpret_cast<__nv_bfloat16*>(xsum_s + (INT4 ? ((p.batch * p.nkb + 3) & ~3) : 0));  // [batch][xstride]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + kSLutBytes);               // [16 warps][kMaxStages]
+  float* red = reinterpret_cast<float*>(bars + kGroups * kSWarps * kMaxStages);      // [groups][RED_GROUP]
+  float* s_ssq = red + kGroups * RED_GROUP;                                          // [16 warps][16]
+  float* s_rstd = s_ssq + kGroups * kSWarps * 16;                                    // [16]
+  float* xsum_s = s_rstd + 16;                                                       // INT4: [batch][nkb]
+  __nv_bfloat16* x_s = reinterpret_cast<__nv_bfloat16*>(xsum_s + (INT4 ? ((p.batch * p.nkb + 3) & ~3) : 0));
+  uint8_t* ring_base = reinterpret_cast<uint8_t*>(x_s) + (((size_t)p.batch * p.xstride * 2 + 127) & ~(size_t)127);
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp_all = tid >> 5;
+  const int grp = warp_all / kSWarps, warp = warp_all % kSWarps;   // warp: k-slice index inside the group
+  const int gtid = tid - grp * kSThreads;                          // thread index inside the group
   const int g = lane >> 2, t = lane & 3;
   const int B = p.batch;
+  const int S = p.stages;
   const uint64_t pol = make_evict_first_policy();
 
-  // this warp's k-blocks [kb0, kb1)
   int kb0, kb1;
   if (INT4) { kb0 = 2 * ((warp * (p.nkb >> 1)) / kSWarps); kb1 = 2 * (((warp + 1) * (p.nkb >> 1)) / kSWarps); }
   else { kb0 = (warp * p.nkb) / kSWarps; kb1 = ((warp + 1) * p.nkb) / kSWarps; }
   const int len = kb1 - kb0;
-  constexpr int REC = INT4 ? 1088 : 576;
-  const int nrec = INT4 ? (p.nkb >> 1) : p.nkb;
+  const int nchunk = (len + C - 1) / C;                            // chunks per pair for this warp
+  const int pair0 = blockIdx.x * kGroups + grp, pstride = gridDim.x * kGroups;
 
-  auto load_item = [&](SItem& it, int pair, int kb) {
-    const int tile0 = p.swiglu ? pair : 2 * pair;
-    const int tile1 = p.swiglu ? pair : 2 * pair + 1;
-    const int rec = INT4 ? (kb >> 1) : kb;
-    const int woff = (INT4 ? (kb & 1) * 512 : 0) + lane * 16;
-    const int soff = (INT4 ? 1024 : 512) + g * 8;
-    const uint8_t* r0 = p.tA + ((int64_t)tile0 * nrec + rec) * REC;
-    it.w0 = ldg_w_v4(r0 + woff, pol);
-    if (!INT4 || !(kb & 1)) it.s0 = ldg_w_v2(r0 + soff, pol);
-    if (tile1 < p.ntiles) {
-      const uint8_t* r1 = p.tB + ((int64_t)tile1 * nrec + rec) * REC;
-      it.w1 = ldg_w_v4(r1 + woff, pol);
-      if (!INT4 || !(kb & 1)) it.s1 = ldg_w_v2(r1 + soff, pol);
-    } else {
-      it.w1 = make_uint4(0u, 0u, 0u, 0u);
-      it.s1 = make_uint2(0u, 0u);
-    }
+  uint8_t* my_ring = ring_base + (size_t)warp_all * S * STAGE;
+  const uint32_t my_ring_u32 = smem_u32(my_ring);
+  const uint32_t my_bars = smem_u32(bars + warp_all * kMaxStages);
+
+  // producer cursor (lane 0 of every warp feeds its own ring)
+  int pr_pair = pair0, pr_cb = kb0, pr_stage = 0;
+  auto produce = [&]() {  // issue the bulk copies of the next chunk into stage pr_stage (caller guarantees it is free)
+    if (len <= 0 || pr_pair >= p.npairs) return;
+    const int nblk = min(C, kb1 - pr_cb);
+    const int tile0 = p.swiglu ? pr_pair : 2 * pr_pair;
+    const int tile1 = p.swiglu ? pr_pair : 2 * pr_pair + 1;
+    const bool has1 = tile1 < p.ntiles;
+    const uint32_t bytes = (uint32_t)nblk * BLK_BYTES;
+    const uint32_t bar = my_bars + pr_stage * 8;
+    const uint32_t dst = my_ring_u32 + pr_stage * STAGE;
+    mbar_expect_tx(bar, has1 ? 2 * bytes : bytes);
+    bulk_g2s(dst, p.tA + ((int64_t)tile0 * p.nkb + pr_cb) * BLK_BYTES, bytes, bar, pol);
+    if (has1) bulk_g2s(dst + STAGE_TILE, p.tB + ((int64_t)tile1 * p.nkb + pr_cb) * BLK_BYTES, bytes, bar, pol);
+    pr_cb += C;
+    if (pr_cb >= kb1) { pr_cb = kb0; pr_pair += pstride; }
+    pr_stage = pr_stage + 1 == S ? 0 : pr_stage + 1;
   };
 
-  // ---- input-independent prologue: first D items in flight, L2 prefetch of the next kernel's weights, LUT ----
-  SItem ring[D];
-#pragma unroll
-  for (int d = 0; d < D; ++d) { ring[d].w0 = ring[d].w1 = make_uint4(0u, 0u, 0u, 0u); ring[d].s0 = ring[d].s1 = make_uint2(0u, 0u); }
-  int ld_pair = blockIdx.x, ld_kb = kb0;
-  auto ld_advance = [&]() { if (++ld_kb >= kb1) { ld_kb = kb0; ld_pair += gridDim.x; } };
-  if (len > 0) {
-#pragma unroll
-    for (int d = 0; d < D; ++d) {
-      if (ld_pair < p.npairs) { load_item(ring[d], ld_pair, ld_kb); ld_advance(); }
+  // ---- input-independent prologue ------------------------------------------------------------------------------
+  if (lane == 0) {
+    for (int s = 0; s < kMaxStages; ++s) mbar_init(my_bars + s * 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    for (int s = 0; s < S; ++s) produce();
+    if (p.pf != nullptr) {  // ask the L2 to fetch the NEXT kernel's weights: CTA share, split over the 16 warps
+      const int64_t per_cta = (((p.pf_bytes + gridDim.x - 1) / gridDim.x) + 2047) & ~(int64_t)2047;
+      const int64_t per_warp = per_cta / (kGroups * kSWarps);  // multiple of 128
+      int64_t beg = (int64_t)blockIdx.x * per_cta + (int64_t)warp_all * per_warp;
+      int64_t end = beg + per_warp;
+      if (end > p.pf_bytes) end = p.pf_bytes & ~(int64_t)15;
+      for (; beg < end; beg += 8192) prefetch_l2_bulk(p.pf + beg, (uint32_t)(end - beg < 8192 ? end - beg : 8192));
     }
   }
-  if (p.pf != nullptr && lane == 0) {
-    // CTA share, split over the 8 warps, in pieces of <= 8 KB (size and address multiples of 16)
-    const int64_t per_cta = (((p.pf_bytes + gridDim.x - 1) / gridDim.x) + 1023) & ~(int64_t)1023;
-    const int64_t per_warp = per_cta / kSWarps;  // multiple of 128
-    int64_t beg = (int64_t)blockIdx.x * per_cta + (int64_t)warp * per_warp;
-    int64_t end = beg + per_warp;
-    if (end > p.pf_bytes) end = p.pf_bytes & ~(int64_t)15;
-    for (; beg < end; beg += 8192) {
-      const int64_t n = end - beg < 8192 ? end - beg : 8192;
-      prefetch_l2_bulk(p.pf + beg, (uint32_t)n);
-    }
-  }
-  for (int i = tid; i < 256 * 32; i += kSThreads) {
+  for (int i = tid; i < 256 * 32; i += kSThreadsAll) {
     const int e = i >> 5, l = i & 31;
     float lo, hi;
     if (INT4) { lo = (float)(e & 15); hi = (float)(e >> 4); }                      // k even = LOW nibble
@@ -167,7 +191,7 @@ __global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const Stream
   const int chunks = (int)(p.K >> 3);
   for (int b = 0; b < B; ++b) {
     float ss = 0.f;
-    for (int c = tid; c < chunks; c += kSThreads) {
+    for (int c = tid; c < chunks; c += kSThreadsAll) {
       uint4 v = *reinterpret_cast<const uint4*>(p.x + (int64_t)b * p.K + c * 8);
       if (p.delta) {
         const uint4 dv = *reinterpret_cast<const uint4*>(p.delta + (int64_t)b * p.K + c * 8);
@@ -184,7 +208,7 @@ __global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const Stream
     }
     if (p.norm_w) {
       ss = warp_sum(ss);
-      if (lane == 0) s_ssq[warp * 16 + b] = ss;
+      if (lane == 0) s_ssq[warp_all * 16 + b] = ss;
     }
   }
   if (p.norm_w) {
@@ -192,13 +216,13 @@ __global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const Stream
     if (tid < B) {
       float tot = 0.f;
 #pragma unroll
-      for (int w = 0; w < kSWarps; ++w) tot += s_ssq[w * 16 + tid];
+      for (int w = 0; w < kGroups * kSWarps; ++w) tot += s_ssq[w * 16 + tid];
       s_rstd[tid] = rsqrtf(tot / (float)p.K + p.eps);
     }
     __syncthreads();
     for (int b = 0; b < B; ++b) {
       const float rstd = s_rstd[b];
-      for (int c = tid; c < chunks; c += kSThreads) {  // same thread owns the same chunk as above
+      for (int c = tid; c < chunks; c += kSThreadsAll) {  // same thread owns the same chunk as above
         uint4 v = *reinterpret_cast<uint4*>(x_s + b * p.xstride + c * 8);
         const uint4 nw = *reinterpret_cast<const uint4*>(p.norm_w + c * 8);
         // weight * (x * rstd), fp32, one cast (rmsnorm.py:24-25)
@@ -212,7 +236,7 @@ __global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const Stream
   }
   __syncthreads();  // x_s and the LUT are published
   if (INT4) {       // per (batch row, k-block) activation sums for the zero-point term
-    for (int i = tid; i < B * p.nkb; i += kSThreads) {
+    for (int i = tid; i < B * p.nkb; i += kSThreadsAll) {
       const int b = i / p.nkb, kb = i % p.nkb;
       const uint32_t* px = reinterpret_cast<const uint32_t*>(x_s + b * p.xstride + kb * 64);
       float s = 0.f;
@@ -237,9 +261,9 @@ __global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const Stream
 #pragma unroll
     for (int i = 0; i < 4; ++i) acc0[nb][i] = acc1[nb][i] = 0.f;
   }
-  uint2 hold0 = make_uint2(0u, 0u), hold1 = make_uint2(0u, 0u);  // INT4: {scale, zero} of the current group
 
-  auto compute = [&](const SItem& it, int kb) {
+  // one k-block of both tiles: w0 / w1 = this lane's 16 B {row g bytes, row g+8 bytes}; s0 / s1 = scale words
+  auto compute = [&](const uint4 w0, const uint4 w1, const uint2 s0, const uint2 s1, int kb) {
     uint32_t xb[NB][8];
 #pragma unroll
     for (int nb = 0; nb < NB; ++nb) {
@@ -264,22 +288,21 @@ __global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const Stream
     for (int j = 0; j < 4; ++j) {
       const uint32_t sel0 = (j & 1) ? 0x5524u : 0x5504u, sel1 = (j & 1) ? 0x5534u : 0x5514u;
       {
-        const uint32_t wa = (j < 2) ? it.w0.x : it.w0.y, wb = (j < 2) ? it.w0.z : it.w0.w;
+        const uint32_t wa = (j < 2) ? w0.x : w0.y, wb = (j < 2) ? w0.z : w0.w;
         const uint32_t a0 = LUT(wa, sel0), a2 = LUT(wa, sel1), a1 = LUT(wb, sel0), a3 = LUT(wb, sel1);
 #pragma unroll
         for (int nb = 0; nb < NB; ++nb) mma16816(p0[nb], a0, a1, a2, a3, xb[nb][2 * j], xb[nb][2 * j + 1]);
       }
       {
-        const uint32_t wa = (j < 2) ? it.w1.x : it.w1.y, wb = (j < 2) ? it.w1.z : it.w1.w;
+        const uint32_t wa = (j < 2) ? w1.x : w1.y, wb = (j < 2) ? w1.z : w1.w;
         const uint32_t a0 = LUT(wa, sel0), a2 = LUT(wa, sel1), a1 = LUT(wb, sel0), a3 = LUT(wb, sel1);
 #pragma unroll
         for (int nb = 0; nb < NB; ++nb) mma16816(p1[nb], a0, a1, a2, a3, xb[nb][2 * j], xb[nb][2 * j + 1]);
       }
     }
     if (INT4) {
-      if (!(kb & 1)) { hold0 = it.s0; hold1 = it.s1; }
-      const __half2 h0a = *reinterpret_cast<const __half2*>(&hold0.x), h0b = *reinterpret_cast<const __half2*>(&hold0.y);
-      const __half2 h1a = *reinterpret_cast<const __half2*>(&hold1.x), h1b = *reinterpret_cast<const __half2*>(&hold1.y);
+      const __half2 h0a = *reinterpret_cast<const __half2*>(&s0.x), h0b = *reinterpret_cast<const __half2*>(&s0.y);
+      const __half2 h1a = *reinterpret_cast<const __half2*>(&s1.x), h1b = *reinterpret_cast<const __half2*>(&s1.y);
       const float s0a = __low2float(h0a), z0a = __high2float(h0a), s0b = __low2float(h0b), z0b = __high2float(h0b);
       const float s1a = __low2float(h1a), z1a = __high2float(h1a), s1b = __low2float(h1b), z1b = __high2float(h1b);
 #pragma unroll
@@ -297,8 +320,8 @@ __global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const Stream
         acc1[nb][3] = fmaf(s1b, p1[nb][3] - z1b * xs1, acc1[nb][3]);
       }
     } else {
-      const float s0a = __uint_as_float(it.s0.x), s0b = __uint_as_float(it.s0.y);
-      const float s1a = __uint_as_float(it.s1.x), s1b = __uint_as_float(it.s1.y);
+      const float s0a = __uint_as_float(s0.x), s0b = __uint_as_float(s0.y);
+      const float s1a = __uint_as_float(s1.x), s1b = __uint_as_float(s1.y);
 #pragma unroll
       for (int nb = 0; nb < NB; ++nb) {
         acc0[nb][0] = fmaf(s0a, p0[nb][0], acc0[nb][0]);
@@ -319,22 +342,39 @@ __global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const Stream
     p.y[(int64_t)c * p.N + n] = __float2bfloat16_rn(h);
   };
 
-  int slot = 0, it_no = 0;
-  for (int pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, ++it_no) {
-    int kb = kb0;
-    while (kb < kb1) {
+  int stage = 0;
+  uint32_t parity = 0;
+  for (int pair = pair0; pair < p.npairs; pair += pstride) {
+    const bool has1 = (p.swiglu ? pair : 2 * pair + 1) < p.ntiles;
+    for (int cb = kb0; cb < kb1; cb += C) {
+      const int nblk = min(C, kb1 - cb);
+      mbar_wait(my_bars + stage * 8, parity);
+      const uint8_t* sp = my_ring + stage * STAGE;
 #pragma unroll
-      for (int d = 0; d < D; ++d) {
-        if (d == slot && kb < kb1) {  // warp-uniform
-          compute(ring[d], kb);
-          if (ld_pair < p.npairs) { load_item(ring[d], ld_pair, ld_kb); ld_advance(); }
-          ++kb;
-          slot = (d + 1 == D) ? 0 : d + 1;
+      for (int b = 0; b < C; ++b) {
+        if (b < nblk) {
+          const int woff = (INT4 ? b * 512 : b * 576) + lane * 16;
+          const int soff = (INT4 ? 1024 : b * 576 + 512) + g * 8;
+          const uint4 w0 = *reinterpret_cast<const uint4*>(sp + woff);
+          const uint2 s0 = *reinterpret_cast<const uint2*>(sp + soff);
+          uint4 w1 = make_uint4(0u, 0u, 0u, 0u);
+          uint2 s1 = make_uint2(0u, 0u);
+          if (has1) {
+            w1 = *reinterpret_cast<const uint4*>(sp + STAGE_TILE + woff);
+            s1 = *reinterpret_cast<const uint2*>(sp + STAGE_TILE + soff);
+          }
+          compute(w0, w1, s0, s1, cb + b);
         }
       }
+      __syncwarp();
+      if (lane == 0) {  // the stage is drained: hand it back to the async proxy and refill it S chunks ahead
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        produce();
+      }
+      if (++stage == S) { stage = 0; parity ^= 1u; }
     }
-    // ---- reduce the 8 k-slices through shared memory (double-buffered: one barrier per pair) ------------------
-    float* rbuf = red + (it_no & 1) * RED_ONE + warp * (2 * 16 * COLS);
+    // ---- reduce the 8 k-slices of this group through shared memory ----------------------------------------------
+    float* rbuf = red + grp * RED_GROUP + warp * (2 * 16 * COLS);
 #pragma unroll
     for (int nb = 0; nb < NB; ++nb) {
       *reinterpret_cast<float2*>(rbuf + g * COLS + 8 * nb + 2 * t) = make_float2(acc0[nb][0], acc0[nb][1]);
@@ -344,10 +384,10 @@ __global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const Stream
 #pragma unroll
       for (int i = 0; i < 4; ++i) acc0[nb][i] = acc1[nb][i] = 0.f;
     }
-    __syncthreads();
-    if (tid < 16 * COLS) {
-      const int r = tid / COLS, c = tid % COLS;
-      const float* rb = red + (it_no & 1) * RED_ONE;
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(kSThreads) : "memory");
+    if (gtid < 16 * COLS) {
+      const int r = gtid / COLS, c = gtid % COLS;
+      const float* rb = red + grp * RED_GROUP;
       float v0 = 0.f, v1 = 0.f;
 #pragma unroll
       for (int w = 0; w < kSWarps; ++w) {
@@ -369,27 +409,21 @@ __global__ void __launch_bounds__(kSThreads, 2) qgemv_stream_kernel(const Stream
         }
       }
     }
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(kSThreads) : "memory");
   }
 }
 
 static std::atomic<int> g_stream_depth{0}, g_stream_occ{0}, g_stream_pf{1};
 
-template <int NB, bool INT4, int D>
-static cudaError_t launch_stream(const StreamParams& p, int gx, size_t smem, cudaStream_t st) {
-  static size_t configured = 0;  // per instantiation: largest dynamic smem size opted into so far
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(qgemv_stream_kernel<NB, INT4, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
-    if (e != cudaSuccess) return e;
-    configured = 227 * 1024;
-  }
-  return launch(qgemv_stream_kernel<NB, INT4, D>, dim3(gx), dim3(kSThreads), smem, st, p);
-}
-
 template <int NB, bool INT4>
-static cudaError_t dispatch_depth(int D, const StreamParams& p, int gx, size_t smem, cudaStream_t st) {
-  if (NB == 1 && D >= 6) return launch_stream<NB, INT4, 6>(p, gx, smem, st);
-  if (D <= 2) return launch_stream<NB, INT4, 2>(p, gx, smem, st);
-  return launch_stream<NB, INT4, 4>(p, gx, smem, st);
+static cudaError_t launch_stream(const StreamParams& p, int gx, size_t smem, cudaStream_t st) {
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(qgemv_stream_kernel<NB, INT4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  return launch(qgemv_stream_kernel<NB, INT4>, dim3(gx), dim3(kSThreadsAll), smem, st, p);
 }
 
 }  // namespace b200
@@ -444,24 +478,28 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
 
   const int NB = a->batch > 8 ? 2 : 1;
   const int COLS = 8 * NB;
-  size_t smem = kSLutBytes + sizeof(float) * (2 * kSWarps * 2 * 16 * COLS + kSWarps * 16 + 16);
-  if (int4) smem += sizeof(float) * (((size_t)a->batch * p.nkb + 3) & ~(size_t)3);
-  smem += (size_t)a->batch * p.xstride * 2;
+  const size_t stage_bytes = 2 * (size_t)kChunkBlocks * (int4 ? 544 : 576);
+  size_t fixed = kSLutBytes + 8 * (size_t)kGroups * kSWarps * kMaxStages +
+                 sizeof(float) * ((size_t)kGroups * kSWarps * 2 * 16 * COLS + kGroups * kSWarps * 16 + 16);
+  if (int4) fixed += sizeof(float) * (((size_t)a->batch * p.nkb + 3) & ~(size_t)3);
+  fixed += ((size_t)a->batch * p.xstride * 2 + 127) & ~(size_t)127;
+  fixed += 128;  // alignment slack of the dynamic shared-memory base
+  int stages = g_stream_depth.load();
+  if (stages < 2 || stages > kMaxStages) stages = 3;
+  while (stages > 2 && fixed + (size_t)kGroups * kSWarps * stages * stage_bytes > 227 * 1024) --stages;
+  const size_t smem = fixed + (size_t)kGroups * kSWarps * stages * stage_bytes;
   if (smem > 227 * 1024) {
     set_error("b200_qgemv_tiled: batch %d x K %lld needs %zu bytes of shared memory (> 227 KB)", a->batch, (long long)a->K, smem);
     return B200_ERR_UNSUPPORTED;
   }
-  int occ = g_stream_occ.load();
-  if (occ < 1 || occ > 2) occ = 1;
-  if (smem > 113 * 1024) occ = 1;
-  int gx = sm_count() * occ;
-  if (gx > p.npairs) gx = p.npairs;
-  int D = g_stream_depth.load();
-  if (D <= 0) D = 4;
+  p.stages = stages;
+  int gx = sm_count();
+  const int cta_pairs = (p.npairs + kGroups - 1) / kGroups;
+  if (gx > cta_pairs) gx = cta_pairs;
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t e;
-  if (int4) e = NB == 2 ? dispatch_depth<2, true>(D, p, gx, smem, st) : dispatch_depth<1, true>(D, p, gx, smem, st);
-  else e = NB == 2 ? dispatch_depth<2, false>(D, p, gx, smem, st) : dispatch_depth<1, false>(D, p, gx, smem, st);
+  if (int4) e = NB == 2 ? launch_stream<2, true>(p, gx, smem, st) : launch_stream<1, true>(p, gx, smem, st);
+  else e = NB == 2 ? launch_stream<2, false>(p, gx, smem, st) : launch_stream<1, false>(p, gx, smem, st);
   if (e != cudaSuccess) {
     set_error("b200_qgemv_tiled: launch failed: %s", cudaGetErrorString(e));
     return B200_ERR_CUDA;
