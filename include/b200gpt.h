@@ -130,7 +130,11 @@ typedef struct b200_qgemv_tiled_args {
   void* y;                 /* (batch, N) bf16 */
   const void* prefetch;
   int64_t prefetch_bytes;
+  void* workspace;         /* zero-initialised once by the caller, >= b200_qgemv_tiled_workspace_bytes(); holds the
+                              partial sums / arrival counters of row pairs cut by a stream-K boundary (self-cleaning) */
+  size_t workspace_bytes;
 } b200_qgemv_tiled_args;
+size_t b200_qgemv_tiled_workspace_bytes(void);
 int b200_qgemv_tiled(const b200_qgemv_tiled_args* args, b200_stream_t stream);
 /* tuning: depth in {0(auto),2,4,6} items loaded ahead per warp; ctas_per_sm in {0(auto),1,2}; l2_prefetch 0/1 */
 int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch);

@@ -36,7 +36,7 @@ class QGemvTiledArgs(ctypes.Structure):
         ("x", c_void_p), ("delta", c_void_p), ("x_out", c_void_p), ("norm_weight", c_void_p),
         ("norm_eps", c_float), ("batch", c_int), ("epilogue", c_int),
         ("bias", c_void_p), ("bias2", c_void_p), ("residual", c_void_p), ("y", c_void_p),
-        ("prefetch", c_void_p), ("prefetch_bytes", c_int64),
+        ("prefetch", c_void_p), ("prefetch_bytes", c_int64), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
     ]
 
 
@@ -74,6 +74,7 @@ _SIGNATURES = {
     "b200_tile_4bit": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p]),
     "b200_untile_4bit": (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "b200_qgemv_tiled": (c_int, [ctypes.POINTER(QGemvTiledArgs), c_void_p]),
+    "b200_qgemv_tiled_workspace_bytes": (c_size_t, []),
     "b200_qgemv_tiled_tune": (c_int, [c_int, c_int, c_int]),
     "b200_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
     "b200_attn_decode_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),

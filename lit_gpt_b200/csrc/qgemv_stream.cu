@@ -42,6 +42,10 @@ struct StreamParams {
   __nv_bfloat16* y;
   int xstride;         // shared-memory row stride of the activation, in bf16 elements (K + 8)
   int stages;          // ring stages per warp (2..4)
+  int upp;             // work units per pair (NF4/FP4: k-blocks; INT4: 128-wide groups)
+  int maxslots;        // stream-K: max groups contributing to one pair
+  float* ws_part;      // [npairs][maxslots][2][16][COLS] partial sums of pairs cut by a group boundary
+  unsigned int* ws_cnt;  // [npairs] arrival counters (self-cleaning)
   const uint8_t* pf;   // L2 prefetch range (next kernel's weights), may be null
   int64_t pf_bytes;
 };
@@ -99,6 +103,29 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol) : "memory");
 }
 
+// Stream-K work split: the (pair, k-unit) space is cut into equal contiguous ranges, one per group of 8 warps, so
+// every SM streams the same number of bytes whatever the shape.  A group walks the segments (pair, [a, b)) of its
+// range; inside a segment the 8 warps split [a, b) evenly.
+struct SegCursor {
+  int cur, end;   // group range, in units
+  int pair, a, b; // current segment: units [a, b) of `pair`
+  int kb0, kb1;   // this warp's k-blocks inside the segment
+};
+__device__ __forceinline__ void seg_load(SegCursor& s, int upp, int bpu, int warp) {
+  s.pair = s.cur / upp;
+  s.a = s.cur - s.pair * upp;
+  const int n = min(upp - s.a, s.end - s.cur);
+  s.b = s.a + n;
+  s.kb0 = bpu * (s.a + (n * warp) / 8);
+  s.kb1 = bpu * (s.a + (n * (warp + 1)) / 8);
+}
+__device__ __forceinline__ bool seg_next(SegCursor& s, int upp, int bpu, int warp) {
+  s.cur += s.b - s.a;
+  if (s.cur >= s.end) return false;
+  seg_load(s, upp, bpu, warp);
+  return true;
+}
+
 constexpr int kGroups = 2;                      // row groups per CTA (each: 8 warps splitting K for one pair)
 constexpr int kSThreadsAll = kGroups * kSThreads;
 constexpr int kChunkBlocks = 2;                 // k-blocks per ring stage (per tile)
@@ -120,7 +147,8 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   float* red = reinterpret_cast<float*>(bars + kGroups * kSWarps * kMaxStages);      // [groups][RED_GROUP]
   float* s_ssq = red + kGroups * RED_GROUP;                                          // [16 warps][16]
   float* s_rstd = s_ssq + kGroups * kSWarps * 16;                                    // [16]
-  float* xsum_s = s_rstd + 16;                                                       // INT4: [batch][nkb]
+  uint32_t* s_flag = reinterpret_cast<uint32_t*>(s_rstd + 16);                       // [groups] (padded to 16)
+  float* xsum_s = s_rstd + 32;                                                       // INT4: [batch][nkb]
   __nv_bfloat16* x_s = reinterpret_cast<__nv_bfloat16*>(xsum_s + (INT4 ? ((p.batch * p.nkb + 3) & ~3) : 0));
   uint8_t* ring_base = reinterpret_cast<uint8_t*>(x_s) + (((size_t)p.batch * p.xstride * 2 + 127) & ~(size_t)127);
 
@@ -132,24 +160,31 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   const int S = p.stages;
   const uint64_t pol = make_evict_first_policy();
 
-  int kb0, kb1;
-  if (INT4) { kb0 = 2 * ((warp * (p.nkb >> 1)) / kSWarps); kb1 = 2 * (((warp + 1) * (p.nkb >> 1)) / kSWarps); }
-  else { kb0 = (warp * p.nkb) / kSWarps; kb1 = ((warp + 1) * p.nkb) / kSWarps; }
-  const int len = kb1 - kb0;
-  const int nchunk = (len + C - 1) / C;                            // chunks per pair for this warp
-  const int pair0 = blockIdx.x * kGroups + grp, pstride = gridDim.x * kGroups;
+  constexpr int BPU = INT4 ? 2 : 1;                                 // k-blocks per work unit
+  const int ngroups = gridDim.x * kGroups, gidx = blockIdx.x * kGroups + grp;
+  const int64_t Wtot = (int64_t)p.npairs * p.upp;
+  auto bnd = [&](int j) -> int { return (int)((Wtot * j) / ngroups); };
+  const int u_begin = bnd(gidx), u_end = bnd(gidx + 1);
 
   uint8_t* my_ring = ring_base + (size_t)warp_all * S * STAGE;
   const uint32_t my_ring_u32 = smem_u32(my_ring);
   const uint32_t my_bars = smem_u32(bars + warp_all * kMaxStages);
 
   // producer cursor (lane 0 of every warp feeds its own ring)
-  int pr_pair = pair0, pr_cb = kb0, pr_stage = 0;
+  SegCursor ps;
+  ps.cur = u_begin; ps.end = u_end; ps.pair = 0; ps.a = ps.b = 0; ps.kb0 = ps.kb1 = 0;
+  bool pr_live = u_begin < u_end;
+  if (pr_live) seg_load(ps, p.upp, BPU, warp);
+  int pr_cb = ps.kb0, pr_stage = 0;
   auto produce = [&]() {  // issue the bulk copies of the next chunk into stage pr_stage (caller guarantees it is free)
-    if (len <= 0 || pr_pair >= p.npairs) return;
-    const int nblk = min(C, kb1 - pr_cb);
-    const int tile0 = p.swiglu ? pr_pair : 2 * pr_pair;
-    const int tile1 = p.swiglu ? pr_pair : 2 * pr_pair + 1;
+    while (pr_live && pr_cb >= ps.kb1) {  // skip exhausted / empty slices
+      pr_live = seg_next(ps, p.upp, BPU, warp);
+      pr_cb = ps.kb0;
+    }
+    if (!pr_live) return;
+    const int nblk = min(C, ps.kb1 - pr_cb);
+    const int tile0 = p.swiglu ? ps.pair : 2 * ps.pair;
+    const int tile1 = p.swiglu ? ps.pair : 2 * ps.pair + 1;
     const bool has1 = tile1 < p.ntiles;
     const uint32_t bytes = (uint32_t)nblk * BLK_BYTES;
     const uint32_t bar = my_bars + pr_stage * 8;
@@ -158,7 +193,6 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     bulk_g2s(dst, p.tA + ((int64_t)tile0 * p.nkb + pr_cb) * BLK_BYTES, bytes, bar, pol);
     if (has1) bulk_g2s(dst + STAGE_TILE, p.tB + ((int64_t)tile1 * p.nkb + pr_cb) * BLK_BYTES, bytes, bar, pol);
     pr_cb += C;
-    if (pr_cb >= kb1) { pr_cb = kb0; pr_pair += pstride; }
     pr_stage = pr_stage + 1 == S ? 0 : pr_stage + 1;
   };
 
@@ -344,10 +378,22 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
 
   int stage = 0;
   uint32_t parity = 0;
-  for (int pair = pair0; pair < p.npairs; pair += pstride) {
+  auto group_of = [&](int u) -> int {  // group whose range contains unit u
+    int j = (int)(((int64_t)u * ngroups) / Wtot);
+    while (j + 1 < ngroups && bnd(j + 1) <= u) ++j;
+    while (j > 0 && bnd(j) > u) --j;
+    return j;
+  };
+
+  SegCursor cs;
+  cs.cur = u_begin; cs.end = u_end; cs.pair = 0; cs.a = cs.b = 0; cs.kb0 = cs.kb1 = 0;
+  bool live = u_begin < u_end;
+  if (live) seg_load(cs, p.upp, BPU, warp);
+  for (; live; live = seg_next(cs, p.upp, BPU, warp)) {
+    const int pair = cs.pair;
     const bool has1 = (p.swiglu ? pair : 2 * pair + 1) < p.ntiles;
-    for (int cb = kb0; cb < kb1; cb += C) {
-      const int nblk = min(C, kb1 - cb);
+    for (int cb = cs.kb0; cb < cs.kb1; cb += C) {
+      const int nblk = min(C, cs.kb1 - cb);
       mbar_wait(my_bars + stage * 8, parity);
       const uint8_t* sp = my_ring + stage * STAGE;
 #pragma unroll
@@ -385,28 +431,57 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
       for (int i = 0; i < 4; ++i) acc0[nb][i] = acc1[nb][i] = 0.f;
     }
     asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(kSThreads) : "memory");
-    if (gtid < 16 * COLS) {
-      const int r = gtid / COLS, c = gtid % COLS;
+    const bool reducer = gtid < 16 * COLS;
+    const int r = gtid / COLS, c = gtid % COLS;
+    float v0 = 0.f, v1 = 0.f;
+    if (reducer) {
       const float* rb = red + grp * RED_GROUP;
-      float v0 = 0.f, v1 = 0.f;
 #pragma unroll
       for (int w = 0; w < kSWarps; ++w) {
         v0 += rb[w * (2 * 16 * COLS) + r * COLS + c];
         v1 += rb[w * (2 * 16 * COLS) + 16 * COLS + r * COLS + c];
       }
-      if (c < B) {
-        if (p.swiglu) {
-          const int64_t n = (int64_t)pair * 16 + r;
-          if (n < p.N) {
-            const float a = round_bf16(v0 + (p.bias ? __bfloat162float(p.bias[n]) : 0.f));
-            const float b = round_bf16(v1 + (p.bias2 ? __bfloat162float(p.bias2[n]) : 0.f));
-            p.y[(int64_t)c * p.N + n] = __float2bfloat16_rn(silu_bf16_s(a) * b);
-          }
-        } else {
-          const int64_t n = (int64_t)pair * 32 + r;
-          if (n < p.N) store_out(n, c, v0);
-          if (n + 16 < p.N) store_out(n + 16, c, v1);
+    }
+    bool do_epi = true;
+    if (cs.a != 0 || cs.b != p.upp) {  // the pair is cut by a group boundary (group-uniform): deterministic hand-off
+      const int jfirst = group_of(pair * p.upp), jlast = group_of(pair * p.upp + p.upp - 1);
+      const int slot = gidx - jfirst, ncontrib = jlast - jfirst + 1;
+      float* part = p.ws_part + ((int64_t)pair * p.maxslots) * (2 * 16 * COLS);
+      if (reducer) {
+        __stcg(part + slot * (2 * 16 * COLS) + r * COLS + c, v0);
+        __stcg(part + slot * (2 * 16 * COLS) + 16 * COLS + r * COLS + c, v1);
+        __threadfence();
+      }
+      asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(kSThreads) : "memory");
+      if (gtid == 0) {
+        const unsigned int old = atomicAdd(p.ws_cnt + pair, 1u);
+        const bool last = old == (unsigned int)(ncontrib - 1);
+        if (last) p.ws_cnt[pair] = 0u;  // self-cleaning for the next launch
+        s_flag[grp] = last ? 1u : 0u;
+      }
+      asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(kSThreads) : "memory");
+      do_epi = s_flag[grp] != 0u;
+      if (do_epi && reducer) {
+        __threadfence();
+        v0 = v1 = 0.f;
+        for (int sl = 0; sl < ncontrib; ++sl) {  // fixed order: deterministic
+          v0 += __ldcg(part + sl * (2 * 16 * COLS) + r * COLS + c);
+          v1 += __ldcg(part + sl * (2 * 16 * COLS) + 16 * COLS + r * COLS + c);
         }
+      }
+    }
+    if (do_epi && reducer && c < B) {
+      if (p.swiglu) {
+        const int64_t n = (int64_t)pair * 16 + r;
+        if (n < p.N) {
+          const float a = round_bf16(v0 + (p.bias ? __bfloat162float(p.bias[n]) : 0.f));
+          const float b = round_bf16(v1 + (p.bias2 ? __bfloat162float(p.bias2[n]) : 0.f));
+          p.y[(int64_t)c * p.N + n] = __float2bfloat16_rn(silu_bf16_s(a) * b);
+        }
+      } else {
+        const int64_t n = (int64_t)pair * 32 + r;
+        if (n < p.N) store_out(n, c, v0);
+        if (n + 16 < p.N) store_out(n + 16, c, v1);
       }
     }
     asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(kSThreads) : "memory");
@@ -431,6 +506,8 @@ static cudaError_t launch_stream(const StreamParams& p, int gx, size_t smem, cud
 using namespace b200;
 
 extern "C" {
+
+size_t b200_qgemv_tiled_workspace_bytes(void) { return (size_t)32 << 20; }
 
 int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch) {
   g_stream_depth = depth;
@@ -480,7 +557,7 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   const int COLS = 8 * NB;
   const size_t stage_bytes = 2 * (size_t)kChunkBlocks * (int4 ? 544 : 576);
   size_t fixed = kSLutBytes + 8 * (size_t)kGroups * kSWarps * kMaxStages +
-                 sizeof(float) * ((size_t)kGroups * kSWarps * 2 * 16 * COLS + kGroups * kSWarps * 16 + 16);
+                 sizeof(float) * ((size_t)kGroups * kSWarps * 2 * 16 * COLS + kGroups * kSWarps * 16 + 32);
   if (int4) fixed += sizeof(float) * (((size_t)a->batch * p.nkb + 3) & ~(size_t)3);
   fixed += ((size_t)a->batch * p.xstride * 2 + 127) & ~(size_t)127;
   fixed += 128;  // alignment slack of the dynamic shared-memory base
@@ -493,9 +570,19 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
     return B200_ERR_UNSUPPORTED;
   }
   p.stages = stages;
+  p.upp = int4 ? p.nkb / 2 : p.nkb;
+  // stream-K: every group gets the same number of work units; keep >= 8 units per group so its 8 warps have work
+  const int64_t Wtot = (int64_t)p.npairs * p.upp;
   int gx = sm_count();
-  const int cta_pairs = (p.npairs + kGroups - 1) / kGroups;
-  if (gx > cta_pairs) gx = cta_pairs;
+  if ((int64_t)gx * kGroups * 8 > Wtot) gx = (int)((Wtot + kGroups * 8 - 1) / (kGroups * 8));
+  const int ngroups = gx * kGroups;
+  p.maxslots = (ngroups + p.npairs - 1) / p.npairs + 1;
+  const size_t cnt_bytes = ((size_t)p.npairs * sizeof(unsigned int) + 255) & ~(size_t)255;
+  const size_t need = cnt_bytes + (size_t)p.npairs * p.maxslots * 2 * 16 * COLS * sizeof(float);
+  B200_CHECK_ARG(a->workspace && a->workspace_bytes >= need, "b200_qgemv_tiled: workspace too small (%zu < %zu)", (size_t)a->workspace_bytes, need);
+  B200_CHECK_ARG((reinterpret_cast<uintptr_t>(a->workspace) & 255) == 0, "b200_qgemv_tiled: workspace must be 256-byte aligned");
+  p.ws_cnt = reinterpret_cast<unsigned int*>(a->workspace);
+  p.ws_part = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(a->workspace) + cnt_bytes);
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t e;
   if (int4) e = NB == 2 ? launch_stream<2, true>(p, gx, smem, st) : launch_stream<1, true>(p, gx, smem, st);

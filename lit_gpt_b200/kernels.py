@@ -169,11 +169,13 @@ def qgemv_tiled(x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, quant_type
     y = out if out is not None else torch.empty((*lead, N), dtype=torch.bfloat16, device=x.device)
     delta, residual, bias, bias2, norm_weight = (_bf16c(delta, "delta"), _bf16c(residual, "residual"), _bf16c(bias, "bias"),
                                                  _bf16c(bias2, "bias2"), _bf16c(norm_weight, "norm_weight"))
+    ws = _ws("qgemv_tiled", x.device, C.load().b200_qgemv_tiled_workspace_bytes())
     args = C.QGemvTiledArgs(
         tiled=tiled.data_ptr(), tiled2=C.ptr(tiled2), qtype=QTYPES[quant_type], blocksize=blocksize, N=N, K=K, x=x.data_ptr(),
         delta=C.ptr(delta), x_out=C.ptr(x_out), norm_weight=C.ptr(norm_weight), norm_eps=norm_eps, batch=batch, epilogue=epilogue,
         bias=C.ptr(bias), bias2=C.ptr(bias2), residual=C.ptr(residual), y=y.data_ptr(), prefetch=C.ptr(prefetch),
-        prefetch_bytes=0 if prefetch is None else prefetch.numel() * prefetch.element_size())
+        prefetch_bytes=0 if prefetch is None else prefetch.numel() * prefetch.element_size(),
+        workspace=ws.data_ptr(), workspace_bytes=ws.numel())
     C.check(C.load().b200_qgemv_tiled(ctypes.byref(args), C.stream_ptr(x.device)), "qgemv_tiled")
     return y
 
