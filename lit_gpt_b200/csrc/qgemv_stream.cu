@@ -2,18 +2,19 @@
 //
 // Replaces bnb.nn.Linear4bit.forward at lit_gpt/model.py:619,656,713,714,716,519.
 //
-// One CTA (8 warps) owns whole output rows: a "pair" is two 16-row tiles (rows 32p..32p+31, or, for SwiGLU, tile p
-// of the gate matrix and tile p of the up matrix), and the 8 warps split K between them, so there is NO split-K
-// across CTAs, no global workspace, no atomics and no fences.  Per 64-wide k-block and tile a warp issues ONE
-// fully coalesced 512-byte load (ld.global.nc, L1 no-allocate, L2 evict-first) plus one 64-byte scale load, kept
-// DEPTH items ahead in registers; the first DEPTH items are requested before griddepcontrol.wait, so under
-// programmatic dependent launch the weight stream of kernel N+1 is already in flight while kernel N drains.
-// Each CTA also issues cp.async.bulk.prefetch.L2 for a caller-given range (the NEXT kernel's weights), which keeps
-// HBM busy across the kernel boundary.
-// Dequant: one PRMT builds a shared-memory address from a packed byte, one conflict-free LDS from a per-lane
-// replicated 256-entry byte -> bf16x2 table returns two code values in mma.sync A-fragment order; mma.sync
-// m16n8k16 (bf16 x bf16 -> fp32) does the MACs against activation B-fragments read from shared memory (shared by
-// the two tiles of a pair); the per-64 absmax (or int4 {scale, zero}) is applied in fp32 per k-block.
+// One persistent CTA per SM owns a contiguous range of 16-row tiles (whole output rows: no split-K across CTAs, no
+// workspace, no atomics).  It walks them two tiles at a time (rows u..u+31, or, for SwiGLU, tile p of the gate and
+// tile p of the up matrix); the 16 consumer warps split K between them.  A 17th PRODUCER warp streams every
+// consumer warp's weights through that warp's private ring of shared-memory stages with cp.async.bulk (TMA) copies
+// signalled on mbarriers (full / empty), so bytes in flight are bounded by shared memory, not by the register
+// scoreboard, and run ahead across tile boundaries and, under programmatic dependent launch, across the previous
+// kernel's tail.  The producer also issues cp.async.bulk.prefetch.L2 for a caller-given range (the NEXT kernel's
+// weights) so HBM stays busy across the kernel boundary.
+// Dequant: ONE PRMT turns a packed byte into the complete shared-memory address of a per-lane replicated
+// 256-entry byte -> bf16x2 table (the table sits at a 64 KB-aligned shared address so no add is needed), one
+// conflict-free LDS returns two code values in mma.sync A-fragment order; mma.sync m16n8k16 (bf16 x bf16 -> fp32)
+// does the MACs against activation B-fragments read from shared memory (shared by the two tiles); the per-64
+// absmax (or int4 {scale, zero}) is applied in fp32 per k-block.
 // Prologue: residual add + RMSNorm of the activation (lit_gpt/rmsnorm.py:19-25, model.py:591) into shared memory.
 // Epilogue: bias / residual add / SwiGLU with the reference's bf16 rounding points (lit_gpt/model.py:712-716).
 #include "common.cuh"
@@ -26,7 +27,7 @@ struct StreamParams {
   int64_t N, K;
   int nkb;             // K / 64
   int ntiles;          // ceil(N / 16)
-  int npairs;          // SwiGLU: ntiles, else ceil(ntiles / 2)
+  int nunits;          // work units: SwiGLU: ntiles (gate tile + up tile each), else ntiles
   int swiglu;
   int qtype;
   const __nv_bfloat16* x;
@@ -41,11 +42,6 @@ struct StreamParams {
   const __nv_bfloat16* residual;
   __nv_bfloat16* y;
   int xstride;         // shared-memory row stride of the activation, in bf16 elements (K + 8)
-  int stages;          // ring stages per warp (2..4)
-  int upp;             // work units per pair (NF4/FP4: k-blocks; INT4: 128-wide groups)
-  int maxslots;        // stream-K: max groups contributing to one pair
-  float* ws_part;      // [npairs][maxslots][2][16][COLS] partial sums of pairs cut by a group boundary
-  unsigned int* ws_cnt;  // [npairs] arrival counters (self-cleaning)
   const uint8_t* pf;   // L2 prefetch range (next kernel's weights), may be null
   int64_t pf_bytes;
 };
@@ -103,114 +99,108 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol) : "memory");
 }
 
-// Stream-K work split: the (pair, k-unit) space is cut into equal contiguous ranges, one per group of 8 warps, so
-// every SM streams the same number of bytes whatever the shape.  A group walks the segments (pair, [a, b)) of its
-// range; inside a segment the 8 warps split [a, b) evenly.
-struct SegCursor {
-  int cur, end;   // group range, in units
-  int pair, a, b; // current segment: units [a, b) of `pair`
-  int kb0, kb1;   // this warp's k-blocks inside the segment
-};
-__device__ __forceinline__ void seg_load(SegCursor& s, int upp, int bpu, int warp) {
-  s.pair = s.cur / upp;
-  s.a = s.cur - s.pair * upp;
-  const int n = min(upp - s.a, s.end - s.cur);
-  s.b = s.a + n;
-  s.kb0 = bpu * (s.a + (n * warp) / 8);
-  s.kb1 = bpu * (s.a + (n * (warp + 1)) / 8);
-}
-__device__ __forceinline__ bool seg_next(SegCursor& s, int upp, int bpu, int warp) {
-  s.cur += s.b - s.a;
-  if (s.cur >= s.end) return false;
-  seg_load(s, upp, bpu, warp);
-  return true;
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
-constexpr int kGroups = 2;                      // row groups per CTA (each: 8 warps splitting K for one pair)
-constexpr int kSThreadsAll = kGroups * kSThreads;
-constexpr int kChunkBlocks = 2;                 // k-blocks per ring stage (per tile)
-constexpr int kMaxStages = 4;
+constexpr int kCW = 16;                          // consumer warps (they split K)
+constexpr int kSThreadsAll = (kCW + 1) * 32;     // + 1 producer warp
+constexpr int kConsumers = kCW * 32;
+constexpr int kMaxStages = 6;
+constexpr int kDynSmem = 227 * 1024;
 
-// Shared-memory layout (dynamic): [LUT 64 KB][mbarriers][red: groups x 8 warps x 2 tiles x 16 x COLS][ssq][rstd][xsum]
-// [x rows][ring: 16 warps x stages x stage_bytes].
+// Shared memory is addressed by ABSOLUTE shared-window addresses so that the dequant table can sit at a 64 KB
+// aligned address L (then `byte << 8 | lane << 2 | L` is assembled by one PRMT):
+//   [b0 .. )        mbarriers, reduction buffer, norm scratch, int4 activation sums, activation rows x_s
+//   [.. L)          ring stages (region A)
+//   [L, L + 64 KB)  table
+//   [L + 64 KB ..)  ring stages (region C)
 template <int NB, bool INT4>
 __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const StreamParams p) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   constexpr int COLS = 8 * NB;
-  constexpr int RED_GROUP = kSWarps * 2 * 16 * COLS;       // floats per group
-  constexpr int C = kChunkBlocks;
-  constexpr int BLK_BYTES = INT4 ? 544 : 576;              // bytes per k-block per tile inside a record stream
-  constexpr int STAGE_TILE = C * BLK_BYTES;                // one tile's part of a stage
-  constexpr int STAGE = 2 * STAGE_TILE;                    // two tiles
-  uint32_t* lut = reinterpret_cast<uint32_t*>(smem_raw);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + kSLutBytes);               // [16 warps][kMaxStages]
-  float* red = reinterpret_cast<float*>(bars + kGroups * kSWarps * kMaxStages);      // [groups][RED_GROUP]
-  float* s_ssq = red + kGroups * RED_GROUP;                                          // [16 warps][16]
-  float* s_rstd = s_ssq + kGroups * kSWarps * 16;                                    // [16]
-  uint32_t* s_flag = reinterpret_cast<uint32_t*>(s_rstd + 16);                       // [groups] (padded to 16)
-  float* xsum_s = s_rstd + 32;                                                       // INT4: [batch][nkb]
-  __nv_bfloat16* x_s = reinterpret_cast<__nv_bfloat16*>(xsum_s + (INT4 ? ((p.batch * p.nkb + 3) & ~3) : 0));
-  uint8_t* ring_base = reinterpret_cast<uint8_t*>(x_s) + (((size_t)p.batch * p.xstride * 2 + 127) & ~(size_t)127);
+  constexpr int REC = INT4 ? 1088 : 576;         // one k-unit (NF4: 64 k, INT4: 128 k) of one tile
+  constexpr int KPU = INT4 ? 2 : 1;              // k-blocks per unit
+  constexpr int STAGE_TILE = kCW * REC;          // 16 consecutive units of one tile
+  constexpr int STAGE = 2 * STAGE_TILE;          // two tiles
+  const uint32_t b0 = smem_u32(smem_raw);
+  uint8_t* const sb = smem_raw - b0;             // generic pointer to shared-window address 0
 
-  const int tid = threadIdx.x, lane = tid & 31, warp_all = tid >> 5;
-  const int grp = warp_all / kSWarps, warp = warp_all % kSWarps;   // warp: k-slice index inside the group
-  const int gtid = tid - grp * kSThreads;                          // thread index inside the group
+  uint32_t off = (b0 + 127u) & ~127u;
+  const uint32_t bars_a = off;          off += 2 * kMaxStages * 8;                      // full[6], empty[6]
+  off = (off + 127u) & ~127u;
+  const uint32_t red_a = off;           off += kCW * 2 * 16 * COLS * 4;                 // [16 warps][2 tiles][16][COLS]
+  const uint32_t ssq_a = off;           off += kCW * 16 * 4;                            // [16 warps][16]
+  const uint32_t rstd_a = off;          off += 16 * 4;
+  const uint32_t xsum_a = off;          off += INT4 ? (((uint32_t)(p.batch * p.nkb) + 3u) & ~3u) * 4 : 0;
+  const uint32_t xs_a = off;            off += (((uint32_t)p.batch * p.xstride * 2) + 127u) & ~127u;
+  const uint32_t ringA_a = off;
+  const uint32_t lut_a = (off + 0xFFFFu) & ~0xFFFFu;                                    // 64 KB aligned
+  const uint32_t ringC_a = lut_a + 0x10000u;
+  const uint32_t end_a = b0 + kDynSmem;
+  const int nA = (int)((lut_a - ringA_a) / STAGE);
+  const int nC = ringC_a < end_a ? (int)((end_a - ringC_a) / STAGE) : 0;
+  const int S = min(kMaxStages, nA + nC);
+  if (S < 2 || ringC_a > end_a) __trap();        // the host sized the launch so that this cannot happen
+  auto stage_addr = [&](int s) -> uint32_t { return s < nC ? ringC_a + s * STAGE : ringA_a + (s - nC) * STAGE; };
+
+  float* red = reinterpret_cast<float*>(sb + red_a);
+  float* s_ssq = reinterpret_cast<float*>(sb + ssq_a);
+  float* s_rstd = reinterpret_cast<float*>(sb + rstd_a);
+  float* xsum_s = reinterpret_cast<float*>(sb + xsum_a);
+  __nv_bfloat16* x_s = reinterpret_cast<__nv_bfloat16*>(sb + xs_a);
+  uint32_t* lut = reinterpret_cast<uint32_t*>(sb + lut_a);
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, t = lane & 3;
   const int B = p.batch;
-  const int S = p.stages;
-  const uint64_t pol = make_evict_first_policy();
+  const int nku = p.nkb / KPU;                                  // k-units per tile
+  const int nrounds = (nku + kCW - 1) / kCW;                    // ring stages consumed per step
+  // this CTA's contiguous range of work units; a step takes two tiles (non-SwiGLU) or one gate/up pair (SwiGLU)
+  const int u0 = (int)(((int64_t)p.nunits * blockIdx.x) / gridDim.x);
+  const int u1 = (int)(((int64_t)p.nunits * (blockIdx.x + 1)) / gridDim.x);
+  const int ustep = p.swiglu ? 1 : 2;
 
-  constexpr int BPU = INT4 ? 2 : 1;                                 // k-blocks per work unit
-  const int ngroups = gridDim.x * kGroups, gidx = blockIdx.x * kGroups + grp;
-  const int64_t Wtot = (int64_t)p.npairs * p.upp;
-  auto bnd = [&](int j) -> int { return (int)((Wtot * j) / ngroups); };
-  const int u_begin = bnd(gidx), u_end = bnd(gidx + 1);
-
-  uint8_t* my_ring = ring_base + (size_t)warp_all * S * STAGE;
-  const uint32_t my_ring_u32 = smem_u32(my_ring);
-  const uint32_t my_bars = smem_u32(bars + warp_all * kMaxStages);
-
-  // producer cursor (lane 0 of every warp feeds its own ring)
-  SegCursor ps;
-  ps.cur = u_begin; ps.end = u_end; ps.pair = 0; ps.a = ps.b = 0; ps.kb0 = ps.kb1 = 0;
-  bool pr_live = u_begin < u_end;
-  if (pr_live) seg_load(ps, p.upp, BPU, warp);
-  int pr_cb = ps.kb0, pr_stage = 0;
-  auto produce = [&]() {  // issue the bulk copies of the next chunk into stage pr_stage (caller guarantees it is free)
-    while (pr_live && pr_cb >= ps.kb1) {  // skip exhausted / empty slices
-      pr_live = seg_next(ps, p.upp, BPU, warp);
-      pr_cb = ps.kb0;
-    }
-    if (!pr_live) return;
-    const int nblk = min(C, ps.kb1 - pr_cb);
-    const int tile0 = p.swiglu ? ps.pair : 2 * ps.pair;
-    const int tile1 = p.swiglu ? ps.pair : 2 * ps.pair + 1;
-    const bool has1 = tile1 < p.ntiles;
-    const uint32_t bytes = (uint32_t)nblk * BLK_BYTES;
-    const uint32_t bar = my_bars + pr_stage * 8;
-    const uint32_t dst = my_ring_u32 + pr_stage * STAGE;
-    mbar_expect_tx(bar, has1 ? 2 * bytes : bytes);
-    bulk_g2s(dst, p.tA + ((int64_t)tile0 * p.nkb + pr_cb) * BLK_BYTES, bytes, bar, pol);
-    if (has1) bulk_g2s(dst + STAGE_TILE, p.tB + ((int64_t)tile1 * p.nkb + pr_cb) * BLK_BYTES, bytes, bar, pol);
-    pr_cb += C;
-    pr_stage = pr_stage + 1 == S ? 0 : pr_stage + 1;
-  };
-
-  // ---- input-independent prologue ------------------------------------------------------------------------------
-  if (lane == 0) {
-    for (int s = 0; s < kMaxStages; ++s) mbar_init(my_bars + s * 8, 1);
+  if (tid == 0) {
+    for (int s = 0; s < kMaxStages; ++s) { mbar_init(bars_a + s * 8, 1); mbar_init(bars_a + (kMaxStages + s) * 8, kCW); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    for (int s = 0; s < S; ++s) produce();
-    if (p.pf != nullptr) {  // ask the L2 to fetch the NEXT kernel's weights: CTA share, split over the 16 warps
-      const int64_t per_cta = (((p.pf_bytes + gridDim.x - 1) / gridDim.x) + 2047) & ~(int64_t)2047;
-      const int64_t per_warp = per_cta / (kGroups * kSWarps);  // multiple of 128
-      int64_t beg = (int64_t)blockIdx.x * per_cta + (int64_t)warp_all * per_warp;
-      int64_t end = beg + per_warp;
-      if (end > p.pf_bytes) end = p.pf_bytes & ~(int64_t)15;
-      for (; beg < end; beg += 8192) prefetch_l2_bulk(p.pf + beg, (uint32_t)(end - beg < 8192 ? end - beg : 8192));
-    }
   }
-  for (int i = tid; i < 256 * 32; i += kSThreadsAll) {
+  __syncthreads();
+
+  if (warp == kCW) {
+    // ================================ PRODUCER WARP (one elected lane) ==========================================
+    if (lane == 0) {
+      const uint64_t pol = make_evict_first_policy();
+      int n = 0;  // global stage counter
+      auto prefetch_next = [&]() {  // ask the L2 to fetch the NEXT kernel's weights (this CTA's share)
+        if (p.pf == nullptr) return;
+        const int64_t per_cta = (((p.pf_bytes + gridDim.x - 1) / gridDim.x) + 127) & ~(int64_t)127;
+        int64_t beg = (int64_t)blockIdx.x * per_cta, end = beg + per_cta;
+        if (end > p.pf_bytes) end = p.pf_bytes & ~(int64_t)15;
+        for (; beg < end; beg += 16384) prefetch_l2_bulk(p.pf + beg, (uint32_t)(end - beg < 16384 ? end - beg : 16384));
+      };
+      for (int u = u0; u < u1; u += ustep) {
+        const int tile0 = u, tile1 = p.swiglu ? u : u + 1;
+        const bool has1 = p.swiglu || tile1 < u1;
+        for (int r = 0; r < nrounds; ++r, ++n) {
+          const int s = n % S;
+          if (n >= S) mbar_wait(bars_a + (kMaxStages + s) * 8, ((n / S) - 1) & 1);
+          const int nu = min(kCW, nku - r * kCW);
+          const uint32_t bytes = (uint32_t)nu * REC;
+          const uint32_t bar = bars_a + s * 8, dst = stage_addr(s);
+          mbar_expect_tx(bar, has1 ? 2 * bytes : bytes);
+          bulk_g2s(dst, p.tA + ((int64_t)tile0 * nku + r * kCW) * REC, bytes, bar, pol);
+          if (has1) bulk_g2s(dst + STAGE_TILE, p.tB + ((int64_t)tile1 * nku + r * kCW) * REC, bytes, bar, pol);
+          if (n + 1 == S) prefetch_next();  // once this kernel's own ring is full
+        }
+      }
+      if (n < S) prefetch_next();
+    }
+    griddep_launch();
+    return;
+  }
+  // ================================== CONSUMER WARPS ===============================================================
+  for (int i = tid; i < 256 * 32; i += kConsumers) {
     const int e = i >> 5, l = i & 31;
     float lo, hi;
     if (INT4) { lo = (float)(e & 15); hi = (float)(e >> 4); }                      // k even = LOW nibble
@@ -225,7 +215,7 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   const int chunks = (int)(p.K >> 3);
   for (int b = 0; b < B; ++b) {
     float ss = 0.f;
-    for (int c = tid; c < chunks; c += kSThreadsAll) {
+    for (int c = tid; c < chunks; c += kConsumers) {
       uint4 v = *reinterpret_cast<const uint4*>(p.x + (int64_t)b * p.K + c * 8);
       if (p.delta) {
         const uint4 dv = *reinterpret_cast<const uint4*>(p.delta + (int64_t)b * p.K + c * 8);
@@ -242,21 +232,21 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     }
     if (p.norm_w) {
       ss = warp_sum(ss);
-      if (lane == 0) s_ssq[warp_all * 16 + b] = ss;
+      if (lane == 0) s_ssq[warp * 16 + b] = ss;
     }
   }
   if (p.norm_w) {
-    __syncthreads();
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
     if (tid < B) {
       float tot = 0.f;
 #pragma unroll
-      for (int w = 0; w < kGroups * kSWarps; ++w) tot += s_ssq[w * 16 + tid];
+      for (int w = 0; w < kCW; ++w) tot += s_ssq[w * 16 + tid];
       s_rstd[tid] = rsqrtf(tot / (float)p.K + p.eps);
     }
-    __syncthreads();
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
     for (int b = 0; b < B; ++b) {
       const float rstd = s_rstd[b];
-      for (int c = tid; c < chunks; c += kSThreadsAll) {  // same thread owns the same chunk as above
+      for (int c = tid; c < chunks; c += kConsumers) {  // same thread owns the same chunk as above
         uint4 v = *reinterpret_cast<uint4*>(x_s + b * p.xstride + c * 8);
         const uint4 nw = *reinterpret_cast<const uint4*>(p.norm_w + c * 8);
         // weight * (x * rstd), fp32, one cast (rmsnorm.py:24-25)
@@ -268,9 +258,9 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
       }
     }
   }
-  __syncthreads();  // x_s and the LUT are published
+  asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");  // x_s and the LUT are published
   if (INT4) {       // per (batch row, k-block) activation sums for the zero-point term
-    for (int i = tid; i < B * p.nkb; i += kSThreadsAll) {
+    for (int i = tid; i < B * p.nkb; i += kConsumers) {
       const int b = i / p.nkb, kb = i % p.nkb;
       const uint32_t* px = reinterpret_cast<const uint32_t*>(x_s + b * p.xstride + kb * 64);
       float s = 0.f;
@@ -278,15 +268,16 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
       for (int j = 0; j < 32; ++j) s += bf16lo(px[j]) + bf16hi(px[j]);
       xsum_s[i] = s;
     }
-    __syncthreads();
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
   }
 
-  // ---- main loop ------------------------------------------------------------------------------------------------
-  const uint32_t lane_off = (uint32_t)lane << 2;
-  const uint8_t* lut_b = reinterpret_cast<const uint8_t*>(lut);
+  // table address = L | byte << 8 | lane << 2, assembled by ONE PRMT (L is 64 KB aligned): picks lane_full.b0,
+  // word.b_i, lane_full.b2, lane_full.b3
+  const uint32_t lane_full = lut_a | ((uint32_t)lane << 2);
   auto LUT = [&](uint32_t word, uint32_t sel) -> uint32_t {
-    // address = (byte_i << 8) | (lane << 2): PRMT picks lane_off.b0, word.b_i, 0, 0
-    return *reinterpret_cast<const uint32_t*>(lut_b + __byte_perm(word, lane_off, sel));
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(__byte_perm(word, lane_full, sel)));
+    return v;
   };
 
   float acc0[NB][4], acc1[NB][4];
@@ -297,7 +288,7 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   }
 
   // one k-block of both tiles: w0 / w1 = this lane's 16 B {row g bytes, row g+8 bytes}; s0 / s1 = scale words
-  auto compute = [&](const uint4 w0, const uint4 w1, const uint2 s0, const uint2 s1, int kb) {
+  auto compute = [&](const uint4 w0, const uint4 w1, const uint2 s0, const uint2 s1, int kb, bool has1) {
     uint32_t xb[NB][8];
 #pragma unroll
     for (int nb = 0; nb < NB; ++nb) {
@@ -320,14 +311,14 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const uint32_t sel0 = (j & 1) ? 0x5524u : 0x5504u, sel1 = (j & 1) ? 0x5534u : 0x5514u;
+      const uint32_t sel0 = (j & 1) ? 0x7624u : 0x7604u, sel1 = (j & 1) ? 0x7634u : 0x7614u;
       {
         const uint32_t wa = (j < 2) ? w0.x : w0.y, wb = (j < 2) ? w0.z : w0.w;
         const uint32_t a0 = LUT(wa, sel0), a2 = LUT(wa, sel1), a1 = LUT(wb, sel0), a3 = LUT(wb, sel1);
 #pragma unroll
         for (int nb = 0; nb < NB; ++nb) mma16816(p0[nb], a0, a1, a2, a3, xb[nb][2 * j], xb[nb][2 * j + 1]);
       }
-      {
+      if (has1) {  // warp-uniform
         const uint32_t wa = (j < 2) ? w1.x : w1.y, wb = (j < 2) ? w1.z : w1.w;
         const uint32_t a0 = LUT(wa, sel0), a2 = LUT(wa, sel1), a1 = LUT(wb, sel0), a3 = LUT(wb, sel1);
 #pragma unroll
@@ -376,51 +367,36 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     p.y[(int64_t)c * p.N + n] = __float2bfloat16_rn(h);
   };
 
-  int stage = 0;
-  uint32_t parity = 0;
-  auto group_of = [&](int u) -> int {  // group whose range contains unit u
-    int j = (int)(((int64_t)u * ngroups) / Wtot);
-    while (j + 1 < ngroups && bnd(j + 1) <= u) ++j;
-    while (j > 0 && bnd(j) > u) --j;
-    return j;
-  };
 
-  SegCursor cs;
-  cs.cur = u_begin; cs.end = u_end; cs.pair = 0; cs.a = cs.b = 0; cs.kb0 = cs.kb1 = 0;
-  bool live = u_begin < u_end;
-  if (live) seg_load(cs, p.upp, BPU, warp);
-  for (; live; live = seg_next(cs, p.upp, BPU, warp)) {
-    const int pair = cs.pair;
-    const bool has1 = (p.swiglu ? pair : 2 * pair + 1) < p.ntiles;
-    for (int cb = cs.kb0; cb < cs.kb1; cb += C) {
-      const int nblk = min(C, cs.kb1 - cb);
-      mbar_wait(my_bars + stage * 8, parity);
-      const uint8_t* sp = my_ring + stage * STAGE;
+  int n = 0;  // global stage counter (same sequence as the producer)
+  for (int u = u0; u < u1; u += ustep) {
+    const int tile1 = p.swiglu ? u : u + 1;
+    const bool has1 = p.swiglu || tile1 < u1;
+    for (int r = 0; r < nrounds; ++r, ++n) {
+      const int s = n % S;
+      const int ku = r * kCW + warp;               // this warp's k-unit in this round
+      mbar_wait(bars_a + s * 8, (n / S) & 1);
+      if (ku < nku) {
+        const uint32_t sp = stage_addr(s) + warp * REC;
 #pragma unroll
-      for (int b = 0; b < C; ++b) {
-        if (b < nblk) {
-          const int woff = (INT4 ? b * 512 : b * 576) + lane * 16;
-          const int soff = (INT4 ? 1024 : b * 576 + 512) + g * 8;
-          const uint4 w0 = *reinterpret_cast<const uint4*>(sp + woff);
-          const uint2 s0 = *reinterpret_cast<const uint2*>(sp + soff);
-          uint4 w1 = make_uint4(0u, 0u, 0u, 0u);
-          uint2 s1 = make_uint2(0u, 0u);
+        for (int b = 0; b < KPU; ++b) {
+          const uint32_t wa = sp + b * 512 + lane * 16, sa = sp + KPU * 512 + g * 8;
+          uint4 w0, w1 = make_uint4(0u, 0u, 0u, 0u);
+          uint2 s0, s1 = make_uint2(0u, 0u);
+          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w0.x), "=r"(w0.y), "=r"(w0.z), "=r"(w0.w) : "r"(wa));
+          asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(s0.x), "=r"(s0.y) : "r"(sa));
           if (has1) {
-            w1 = *reinterpret_cast<const uint4*>(sp + STAGE_TILE + woff);
-            s1 = *reinterpret_cast<const uint2*>(sp + STAGE_TILE + soff);
+            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w1.x), "=r"(w1.y), "=r"(w1.z), "=r"(w1.w) : "r"(wa + STAGE_TILE));
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(s1.x), "=r"(s1.y) : "r"(sa + STAGE_TILE));
           }
-          compute(w0, w1, s0, s1, cb + b);
+          compute(w0, w1, s0, s1, ku * KPU + b, has1);
         }
       }
       __syncwarp();
-      if (lane == 0) {  // the stage is drained: hand it back to the async proxy and refill it S chunks ahead
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        produce();
-      }
-      if (++stage == S) { stage = 0; parity ^= 1u; }
+      if (lane == 0) mbar_arrive(bars_a + (kMaxStages + s) * 8);  // this warp is done with the stage
     }
-    // ---- reduce the 8 k-slices of this group through shared memory ----------------------------------------------
-    float* rbuf = red + grp * RED_GROUP + warp * (2 * 16 * COLS);
+    // ---- reduce the 16 k-slices through shared memory -------------------------------------------------------------
+    float* rbuf = red + warp * (2 * 16 * COLS);
 #pragma unroll
     for (int nb = 0; nb < NB; ++nb) {
       *reinterpret_cast<float2*>(rbuf + g * COLS + 8 * nb + 2 * t) = make_float2(acc0[nb][0], acc0[nb][1]);
@@ -430,75 +406,44 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
 #pragma unroll
       for (int i = 0; i < 4; ++i) acc0[nb][i] = acc1[nb][i] = 0.f;
     }
-    asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(kSThreads) : "memory");
-    const bool reducer = gtid < 16 * COLS;
-    const int r = gtid / COLS, c = gtid % COLS;
-    float v0 = 0.f, v1 = 0.f;
-    if (reducer) {
-      const float* rb = red + grp * RED_GROUP;
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+    if (tid < 2 * 16 * COLS) {  // one thread per (tile, row, batch column)
+      const int tl = tid / (16 * COLS), r = (tid / COLS) % 16, c = tid % COLS;
+      float v = 0.f;
 #pragma unroll
-      for (int w = 0; w < kSWarps; ++w) {
-        v0 += rb[w * (2 * 16 * COLS) + r * COLS + c];
-        v1 += rb[w * (2 * 16 * COLS) + 16 * COLS + r * COLS + c];
-      }
-    }
-    bool do_epi = true;
-    if (cs.a != 0 || cs.b != p.upp) {  // the pair is cut by a group boundary (group-uniform): deterministic hand-off
-      const int jfirst = group_of(pair * p.upp), jlast = group_of(pair * p.upp + p.upp - 1);
-      const int slot = gidx - jfirst, ncontrib = jlast - jfirst + 1;
-      float* part = p.ws_part + ((int64_t)pair * p.maxslots) * (2 * 16 * COLS);
-      if (reducer) {
-        __stcg(part + slot * (2 * 16 * COLS) + r * COLS + c, v0);
-        __stcg(part + slot * (2 * 16 * COLS) + 16 * COLS + r * COLS + c, v1);
-        __threadfence();
-      }
-      asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(kSThreads) : "memory");
-      if (gtid == 0) {
-        const unsigned int old = atomicAdd(p.ws_cnt + pair, 1u);
-        const bool last = old == (unsigned int)(ncontrib - 1);
-        if (last) p.ws_cnt[pair] = 0u;  // self-cleaning for the next launch
-        s_flag[grp] = last ? 1u : 0u;
-      }
-      asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(kSThreads) : "memory");
-      do_epi = s_flag[grp] != 0u;
-      if (do_epi && reducer) {
-        __threadfence();
-        v0 = v1 = 0.f;
-        for (int sl = 0; sl < ncontrib; ++sl) {  // fixed order: deterministic
-          v0 += __ldcg(part + sl * (2 * 16 * COLS) + r * COLS + c);
-          v1 += __ldcg(part + sl * (2 * 16 * COLS) + 16 * COLS + r * COLS + c);
-        }
-      }
-    }
-    if (do_epi && reducer && c < B) {
+      for (int w = 0; w < kCW; ++w) v += red[w * (2 * 16 * COLS) + tl * 16 * COLS + r * COLS + c];
       if (p.swiglu) {
-        const int64_t n = (int64_t)pair * 16 + r;
-        if (n < p.N) {
-          const float a = round_bf16(v0 + (p.bias ? __bfloat162float(p.bias[n]) : 0.f));
-          const float b = round_bf16(v1 + (p.bias2 ? __bfloat162float(p.bias2[n]) : 0.f));
-          p.y[(int64_t)c * p.N + n] = __float2bfloat16_rn(silu_bf16_s(a) * b);
+        // gate (tile 0) and up (tile 1) values of the same row meet in the gate thread through shared memory
+        if (tl == 1) red[16 * COLS + r * COLS + c] = v;  // warp 0's tile-1 slot: already consumed by this very thread
+        asm volatile("bar.sync 2, %0;" ::"n"(2 * 16 * COLS) : "memory");
+        if (tl == 0 && c < B) {
+          const int64_t nrow = (int64_t)u * 16 + r;
+          if (nrow < p.N) {
+            const float a = round_bf16(v + (p.bias ? __bfloat162float(p.bias[nrow]) : 0.f));
+            const float b = round_bf16(red[16 * COLS + r * COLS + c] + (p.bias2 ? __bfloat162float(p.bias2[nrow]) : 0.f));
+            p.y[(int64_t)c * p.N + nrow] = __float2bfloat16_rn(silu_bf16_s(a) * b);
+          }
         }
-      } else {
-        const int64_t n = (int64_t)pair * 32 + r;
-        if (n < p.N) store_out(n, c, v0);
-        if (n + 16 < p.N) store_out(n + 16, c, v1);
+      } else if (c < B && (tl == 0 || has1)) {
+        const int64_t nrow = (int64_t)(u + tl) * 16 + r;
+        if (nrow < p.N) store_out(nrow, c, v);
       }
     }
-    asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(kSThreads) : "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
   }
 }
 
 static std::atomic<int> g_stream_depth{0}, g_stream_occ{0}, g_stream_pf{1};
 
 template <int NB, bool INT4>
-static cudaError_t launch_stream(const StreamParams& p, int gx, size_t smem, cudaStream_t st) {
+static cudaError_t launch_stream(const StreamParams& p, int gx, cudaStream_t st) {
   static bool configured = false;  // per instantiation
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(qgemv_stream_kernel<NB, INT4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+    cudaError_t e = cudaFuncSetAttribute(qgemv_stream_kernel<NB, INT4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDynSmem);
     if (e != cudaSuccess) return e;
     configured = true;
   }
-  return launch(qgemv_stream_kernel<NB, INT4>, dim3(gx), dim3(kSThreadsAll), smem, st, p);
+  return launch(qgemv_stream_kernel<NB, INT4>, dim3(gx), dim3(kSThreadsAll), (size_t)kDynSmem, st, p);
 }
 
 }  // namespace b200
@@ -507,7 +452,7 @@ using namespace b200;
 
 extern "C" {
 
-size_t b200_qgemv_tiled_workspace_bytes(void) { return (size_t)32 << 20; }
+size_t b200_qgemv_tiled_workspace_bytes(void) { return 256; }  // no workspace is needed any more (kept for ABI)
 
 int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch) {
   g_stream_depth = depth;
@@ -539,7 +484,7 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   p.tB = swiglu ? reinterpret_cast<const uint8_t*>(a->tiled2) : p.tA;
   p.N = a->N; p.K = a->K; p.nkb = (int)(a->K / 64);
   p.ntiles = (int)((a->N + 15) / 16);
-  p.npairs = swiglu ? p.ntiles : (p.ntiles + 1) / 2;
+  p.nunits = p.ntiles;
   p.swiglu = swiglu; p.qtype = a->qtype;
   p.x = reinterpret_cast<const __nv_bfloat16*>(a->x);
   p.delta = reinterpret_cast<const __nv_bfloat16*>(a->delta);
@@ -555,38 +500,26 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
 
   const int NB = a->batch > 8 ? 2 : 1;
   const int COLS = 8 * NB;
-  const size_t stage_bytes = 2 * (size_t)kChunkBlocks * (int4 ? 544 : 576);
-  size_t fixed = kSLutBytes + 8 * (size_t)kGroups * kSWarps * kMaxStages +
-                 sizeof(float) * ((size_t)kGroups * kSWarps * 2 * 16 * COLS + kGroups * kSWarps * 16 + 32);
-  if (int4) fixed += sizeof(float) * (((size_t)a->batch * p.nkb + 3) & ~(size_t)3);
-  fixed += ((size_t)a->batch * p.xstride * 2 + 127) & ~(size_t)127;
-  fixed += 128;  // alignment slack of the dynamic shared-memory base
-  int stages = g_stream_depth.load();
-  if (stages < 2 || stages > kMaxStages) stages = 3;
-  while (stages > 2 && fixed + (size_t)kGroups * kSWarps * stages * stage_bytes > 227 * 1024) --stages;
-  const size_t smem = fixed + (size_t)kGroups * kSWarps * stages * stage_bytes;
-  if (smem > 227 * 1024) {
-    set_error("b200_qgemv_tiled: batch %d x K %lld needs %zu bytes of shared memory (> 227 KB)", a->batch, (long long)a->K, smem);
+  // mirror of the kernel's shared-memory carve-up (assuming the dynamic window starts within the first 1 KB)
+  const size_t stage = 2 * (size_t)kCW * (int4 ? 1088 : 576);
+  size_t off = 1024 + 128 + 128;
+  off += (size_t)kCW * 2 * 16 * COLS * 4 + kCW * 16 * 4 + 16 * 4;
+  if (int4) off += ((((size_t)a->batch * p.nkb) + 3) & ~(size_t)3) * 4;
+  off += (((size_t)a->batch * p.xstride * 2) + 127) & ~(size_t)127;
+  const size_t lut_at = (off + 0xFFFF) & ~(size_t)0xFFFF, ring_c = lut_at + 0x10000, end = 1024 + (size_t)kDynSmem;
+  const size_t slots = (lut_at - off) / stage + (ring_c < end ? (end - ring_c) / stage : 0);
+  if (ring_c > end || slots < 2) {
+    set_error("b200_qgemv_tiled: batch %d x K %lld does not fit the kernel's shared memory plan (activation rows need %zu bytes)",
+              a->batch, (long long)a->K, (size_t)a->batch * p.xstride * 2);
     return B200_ERR_UNSUPPORTED;
   }
-  p.stages = stages;
-  p.upp = int4 ? p.nkb / 2 : p.nkb;
-  // stream-K: every group gets the same number of work units; keep >= 8 units per group so its 8 warps have work
-  const int64_t Wtot = (int64_t)p.npairs * p.upp;
+  const int steps = swiglu ? p.nunits : (p.nunits + 1) / 2;
   int gx = sm_count();
-  if ((int64_t)gx * kGroups * 8 > Wtot) gx = (int)((Wtot + kGroups * 8 - 1) / (kGroups * 8));
-  const int ngroups = gx * kGroups;
-  p.maxslots = (ngroups + p.npairs - 1) / p.npairs + 1;
-  const size_t cnt_bytes = ((size_t)p.npairs * sizeof(unsigned int) + 255) & ~(size_t)255;
-  const size_t need = cnt_bytes + (size_t)p.npairs * p.maxslots * 2 * 16 * COLS * sizeof(float);
-  B200_CHECK_ARG(a->workspace && a->workspace_bytes >= need, "b200_qgemv_tiled: workspace too small (%zu < %zu)", (size_t)a->workspace_bytes, need);
-  B200_CHECK_ARG((reinterpret_cast<uintptr_t>(a->workspace) & 255) == 0, "b200_qgemv_tiled: workspace must be 256-byte aligned");
-  p.ws_cnt = reinterpret_cast<unsigned int*>(a->workspace);
-  p.ws_part = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(a->workspace) + cnt_bytes);
+  if (gx > steps) gx = steps;
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t e;
-  if (int4) e = NB == 2 ? launch_stream<2, true>(p, gx, smem, st) : launch_stream<1, true>(p, gx, smem, st);
-  else e = NB == 2 ? launch_stream<2, false>(p, gx, smem, st) : launch_stream<1, false>(p, gx, smem, st);
+  if (int4) e = NB == 2 ? launch_stream<2, true>(p, gx, st) : launch_stream<1, true>(p, gx, st);
+  else e = NB == 2 ? launch_stream<2, false>(p, gx, st) : launch_stream<1, false>(p, gx, st);
   if (e != cudaSuccess) {
     set_error("b200_qgemv_tiled: launch failed: %s", cudaGetErrorString(e));
     return B200_ERR_CUDA;
