@@ -42,6 +42,8 @@ struct StreamParams {
   const __nv_bfloat16* residual;
   __nv_bfloat16* y;
   int xstride;         // shared-memory row stride of the activation, in bf16 elements (K + 8)
+  int red_bufs;        // reduction buffers (host-chosen: 2 when the ring still gets >= 3 stages, else 1)
+  int debug;           // 1: consumers skip the dequant/MMA work (streaming ceiling measurement only)
   const uint8_t* pf;   // L2 prefetch range (next kernel's weights), may be null
   int64_t pf_bytes;
 };
@@ -51,7 +53,7 @@ constexpr int kSWarps = 8;
 constexpr int kSLutBytes = 256 * 256;  // entry e, lane l at byte e*256 + l*4
 
 __device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
-  asm volatile(
+  asm(  // not volatile: a pure function of its operands, ptxas may interleave it with the table look-ups
       "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
       : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
@@ -129,7 +131,8 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   uint32_t off = (b0 + 127u) & ~127u;
   const uint32_t bars_a = off;          off += 2 * kMaxStages * 8;                      // full[6], empty[6]
   off = (off + 127u) & ~127u;
-  const uint32_t red_a = off;           off += kCW * 2 * 16 * COLS * 4;                 // [16 warps][2 tiles][16][COLS]
+  const int RED_BUFS = p.red_bufs;            // 2: double-buffered (one barrier per step); 1 when shared memory is short
+  const uint32_t red_a = off;           off += RED_BUFS * kCW * 2 * 16 * COLS * 4;      // [buffers][16 warps][2 tiles][16][COLS]
   const uint32_t ssq_a = off;           off += kCW * 16 * 4;                            // [16 warps][16]
   const uint32_t rstd_a = off;          off += 16 * 4;
   const uint32_t xsum_a = off;          off += INT4 ? (((uint32_t)(p.batch * p.nkb) + 3u) & ~3u) * 4 : 0;
@@ -171,7 +174,8 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     // ================================ PRODUCER WARP (one elected lane) ==========================================
     if (lane == 0) {
       const uint64_t pol = make_evict_first_policy();
-      int n = 0;  // global stage counter
+      int n = 0, ps = 0;          // global stage counter, ring slot
+      uint32_t pph = 1;           // parity to wait for on the slot's EMPTY barrier (first lap: no wait)
       auto prefetch_next = [&]() {  // ask the L2 to fetch the NEXT kernel's weights (this CTA's share)
         if (p.pf == nullptr) return;
         const int64_t per_cta = (((p.pf_bytes + gridDim.x - 1) / gridDim.x) + 127) & ~(int64_t)127;
@@ -183,15 +187,15 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
         const int tile0 = u, tile1 = p.swiglu ? u : u + 1;
         const bool has1 = p.swiglu || tile1 < u1;
         for (int r = 0; r < nrounds; ++r, ++n) {
-          const int s = n % S;
-          if (n >= S) mbar_wait(bars_a + (kMaxStages + s) * 8, ((n / S) - 1) & 1);
+          if (n >= S) mbar_wait(bars_a + (kMaxStages + ps) * 8, pph);
           const int nu = min(kCW, nku - r * kCW);
           const uint32_t bytes = (uint32_t)nu * REC;
-          const uint32_t bar = bars_a + s * 8, dst = stage_addr(s);
+          const uint32_t bar = bars_a + ps * 8, dst = stage_addr(ps);
           mbar_expect_tx(bar, has1 ? 2 * bytes : bytes);
           bulk_g2s(dst, p.tA + ((int64_t)tile0 * nku + r * kCW) * REC, bytes, bar, pol);
           if (has1) bulk_g2s(dst + STAGE_TILE, p.tB + ((int64_t)tile1 * nku + r * kCW) * REC, bytes, bar, pol);
           if (n + 1 == S) prefetch_next();  // once this kernel's own ring is full
+          if (++ps == S) { ps = 0; pph ^= 1u; }
         }
       }
       if (n < S) prefetch_next();
@@ -276,7 +280,7 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   const uint32_t lane_full = lut_a | ((uint32_t)lane << 2);
   auto LUT = [&](uint32_t word, uint32_t sel) -> uint32_t {
     uint32_t v;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(__byte_perm(word, lane_full, sel)));
+    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(__byte_perm(word, lane_full, sel)));  // table is read-only: not volatile
     return v;
   };
 
@@ -288,7 +292,7 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   }
 
   // one k-block of both tiles: w0 / w1 = this lane's 16 B {row g bytes, row g+8 bytes}; s0 / s1 = scale words
-  auto compute = [&](const uint4 w0, const uint4 w1, const uint2 s0, const uint2 s1, int kb, bool has1) {
+  auto compute = [&](const uint4 w0, const uint4 w1, const uint2 s0, const uint2 s1, int kb) {
     uint32_t xb[NB][8];
 #pragma unroll
     for (int nb = 0; nb < NB; ++nb) {
@@ -318,7 +322,7 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
 #pragma unroll
         for (int nb = 0; nb < NB; ++nb) mma16816(p0[nb], a0, a1, a2, a3, xb[nb][2 * j], xb[nb][2 * j + 1]);
       }
-      if (has1) {  // warp-uniform
+      {  // tile 1 is computed even when absent (stale stage bytes, result never stored): no branch in the hot block
         const uint32_t wa = (j < 2) ? w1.x : w1.y, wb = (j < 2) ? w1.z : w1.w;
         const uint32_t a0 = LUT(wa, sel0), a2 = LUT(wa, sel1), a1 = LUT(wb, sel0), a3 = LUT(wb, sel1);
 #pragma unroll
@@ -368,68 +372,98 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   };
 
 
-  int n = 0;  // global stage counter (same sequence as the producer)
-  for (int u = u0; u < u1; u += ustep) {
-    const int tile1 = p.swiglu ? u : u + 1;
-    const bool has1 = p.swiglu || tile1 < u1;
-    for (int r = 0; r < nrounds; ++r, ++n) {
-      const int s = n % S;
-      const int ku = r * kCW + warp;               // this warp's k-unit in this round
-      mbar_wait(bars_a + s * 8, (n / S) & 1);
-      if (ku < nku) {
-        const uint32_t sp = stage_addr(s) + warp * REC;
+  // Register-level software pipeline over the flattened (step, round) sequence: the shared-memory stage of round
+  // i+1 is read into registers before round i is computed, and a stage is handed back to the producer one round
+  // after it was read (its loads have certainly completed by then).
+  constexpr int RED_ONE = kCW * 2 * 16 * COLS;
+  const int nsteps = (u1 - u0 + ustep - 1) / ustep;
+  const int total = nsteps * nrounds;
+  uint4 c0[KPU], c1[KPU], n0[KPU], n1[KPU];
+  uint2 cs0, cs1, ns0, ns1;
+  int ls = 0;              // ring slot of the next stage to read
+  uint32_t lph = 0;        // its FULL-barrier parity
+  auto read_stage = [&](int r, uint4 (&a0)[KPU], uint4 (&a1)[KPU], uint2& b0v, uint2& b1v) {
+    mbar_wait(bars_a + ls * 8, lph);
+    const int ku = r * kCW + warp;
+    if (ku < nku) {
+      const uint32_t sp = stage_addr(ls) + warp * REC;
+      const uint32_t sa = sp + KPU * 512 + g * 8;
 #pragma unroll
-        for (int b = 0; b < KPU; ++b) {
-          const uint32_t wa = sp + b * 512 + lane * 16, sa = sp + KPU * 512 + g * 8;
-          uint4 w0, w1 = make_uint4(0u, 0u, 0u, 0u);
-          uint2 s0, s1 = make_uint2(0u, 0u);
-          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w0.x), "=r"(w0.y), "=r"(w0.z), "=r"(w0.w) : "r"(wa));
-          asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(s0.x), "=r"(s0.y) : "r"(sa));
-          if (has1) {
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w1.x), "=r"(w1.y), "=r"(w1.z), "=r"(w1.w) : "r"(wa + STAGE_TILE));
-            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(s1.x), "=r"(s1.y) : "r"(sa + STAGE_TILE));
+      for (int b = 0; b < KPU; ++b) {
+        const uint32_t wa = sp + b * 512 + lane * 16;
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(a0[b].x), "=r"(a0[b].y), "=r"(a0[b].z), "=r"(a0[b].w) : "r"(wa));
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(a1[b].x), "=r"(a1[b].y), "=r"(a1[b].z), "=r"(a1[b].w) : "r"(wa + STAGE_TILE));
+      }
+      asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b0v.x), "=r"(b0v.y) : "r"(sa));
+      asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(b1v.x), "=r"(b1v.y) : "r"(sa + STAGE_TILE));
+    }
+    if (++ls == S) { ls = 0; lph ^= 1u; }
+  };
+#pragma unroll
+  for (int b = 0; b < KPU; ++b) c0[b] = c1[b] = n0[b] = n1[b] = make_uint4(0u, 0u, 0u, 0u);
+  cs0 = cs1 = ns0 = ns1 = make_uint2(0u, 0u);
+
+  const int nku_c = p.debug == 1 ? 0 : nku;  // debug: stream only, no dequant/MMA work
+  int rs = 0;  // ring slot to release next (trails the read slot by one round)
+  int u = u0, r = 0, it = 0;
+  bool has1 = p.swiglu || u + 1 < u1;
+  if (total > 0) read_stage(0, c0, c1, cs0, cs1);
+  for (int i = 0; i < total; ++i) {
+    int nu_ = u, nr = r + 1;  // position of round i+1
+    if (nr == nrounds) { nr = 0; nu_ = u + ustep; }
+    const bool nhas1 = p.swiglu || nu_ + 1 < u1;
+    if (i + 1 < total) read_stage(nr, n0, n1, ns0, ns1);
+    const int ku = r * kCW + warp;
+    if (ku < nku_c) {
+#pragma unroll
+      for (int b = 0; b < KPU; ++b) compute(c0[b], c1[b], cs0, cs1, ku * KPU + b);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bars_a + (kMaxStages + rs) * 8);  // round i's stage: read one iteration ago
+    if (++rs == S) rs = 0;
+#pragma unroll
+    for (int b = 0; b < KPU; ++b) { c0[b] = n0[b]; c1[b] = n1[b]; }
+    cs0 = ns0; cs1 = ns1;
+    if (nr == 0) {
+      // ---- end of a step: reduce the 16 k-slices through shared memory (double-buffered: one barrier per step) ---
+      float* rbuf = red + (RED_BUFS == 2 ? (it & 1) : 0) * RED_ONE + warp * (2 * 16 * COLS);
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) {
+        *reinterpret_cast<float2*>(rbuf + g * COLS + 8 * nb + 2 * t) = make_float2(acc0[nb][0], acc0[nb][1]);
+        *reinterpret_cast<float2*>(rbuf + (g + 8) * COLS + 8 * nb + 2 * t) = make_float2(acc0[nb][2], acc0[nb][3]);
+        *reinterpret_cast<float2*>(rbuf + 16 * COLS + g * COLS + 8 * nb + 2 * t) = make_float2(acc1[nb][0], acc1[nb][1]);
+        *reinterpret_cast<float2*>(rbuf + 16 * COLS + (g + 8) * COLS + 8 * nb + 2 * t) = make_float2(acc1[nb][2], acc1[nb][3]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) acc0[nb][k] = acc1[nb][k] = 0.f;
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+      if (tid < 2 * 16 * COLS) {  // one thread per (tile, row, batch column)
+        float* rb = red + (RED_BUFS == 2 ? (it & 1) : 0) * RED_ONE;
+        const int tl = tid / (16 * COLS), rr = (tid / COLS) % 16, c = tid % COLS;
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < kCW; ++w) v += rb[w * (2 * 16 * COLS) + tl * 16 * COLS + rr * COLS + c];
+        if (p.swiglu) {
+          // gate (tile 0) and up (tile 1) values of the same row meet in the gate thread through shared memory
+          if (tl == 1) rb[16 * COLS + rr * COLS + c] = v;  // warp 0's tile-1 slot: only this thread ever reads it
+          asm volatile("bar.sync 2, %0;" ::"n"(2 * 16 * COLS) : "memory");
+          if (tl == 0 && c < B) {
+            const int64_t nrow = (int64_t)u * 16 + rr;
+            if (nrow < p.N) {
+              const float a = round_bf16(v + (p.bias ? __bfloat162float(p.bias[nrow]) : 0.f));
+              const float b = round_bf16(rb[16 * COLS + rr * COLS + c] + (p.bias2 ? __bfloat162float(p.bias2[nrow]) : 0.f));
+              p.y[(int64_t)c * p.N + nrow] = __float2bfloat16_rn(silu_bf16_s(a) * b);
+            }
           }
-          compute(w0, w1, s0, s1, ku * KPU + b, has1);
+        } else if (c < B && (tl == 0 || has1)) {
+          const int64_t nrow = (int64_t)(u + tl) * 16 + rr;
+          if (nrow < p.N) store_out(nrow, c, v);
         }
       }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bars_a + (kMaxStages + s) * 8);  // this warp is done with the stage
+      if (RED_BUFS == 1) asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+      ++it;
     }
-    // ---- reduce the 16 k-slices through shared memory -------------------------------------------------------------
-    float* rbuf = red + warp * (2 * 16 * COLS);
-#pragma unroll
-    for (int nb = 0; nb < NB; ++nb) {
-      *reinterpret_cast<float2*>(rbuf + g * COLS + 8 * nb + 2 * t) = make_float2(acc0[nb][0], acc0[nb][1]);
-      *reinterpret_cast<float2*>(rbuf + (g + 8) * COLS + 8 * nb + 2 * t) = make_float2(acc0[nb][2], acc0[nb][3]);
-      *reinterpret_cast<float2*>(rbuf + 16 * COLS + g * COLS + 8 * nb + 2 * t) = make_float2(acc1[nb][0], acc1[nb][1]);
-      *reinterpret_cast<float2*>(rbuf + 16 * COLS + (g + 8) * COLS + 8 * nb + 2 * t) = make_float2(acc1[nb][2], acc1[nb][3]);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) acc0[nb][i] = acc1[nb][i] = 0.f;
-    }
-    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
-    if (tid < 2 * 16 * COLS) {  // one thread per (tile, row, batch column)
-      const int tl = tid / (16 * COLS), r = (tid / COLS) % 16, c = tid % COLS;
-      float v = 0.f;
-#pragma unroll
-      for (int w = 0; w < kCW; ++w) v += red[w * (2 * 16 * COLS) + tl * 16 * COLS + r * COLS + c];
-      if (p.swiglu) {
-        // gate (tile 0) and up (tile 1) values of the same row meet in the gate thread through shared memory
-        if (tl == 1) red[16 * COLS + r * COLS + c] = v;  // warp 0's tile-1 slot: already consumed by this very thread
-        asm volatile("bar.sync 2, %0;" ::"n"(2 * 16 * COLS) : "memory");
-        if (tl == 0 && c < B) {
-          const int64_t nrow = (int64_t)u * 16 + r;
-          if (nrow < p.N) {
-            const float a = round_bf16(v + (p.bias ? __bfloat162float(p.bias[nrow]) : 0.f));
-            const float b = round_bf16(red[16 * COLS + r * COLS + c] + (p.bias2 ? __bfloat162float(p.bias2[nrow]) : 0.f));
-            p.y[(int64_t)c * p.N + nrow] = __float2bfloat16_rn(silu_bf16_s(a) * b);
-          }
-        }
-      } else if (c < B && (tl == 0 || has1)) {
-        const int64_t nrow = (int64_t)(u + tl) * 16 + r;
-        if (nrow < p.N) store_out(nrow, c, v);
-      }
-    }
-    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+    u = nu_; r = nr; has1 = nhas1;
   }
 }
 
@@ -496,19 +530,24 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   p.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual);
   p.y = reinterpret_cast<__nv_bfloat16*>(a->y);
   p.xstride = (int)a->K + 8;
+  p.debug = g_stream_depth.load() == 99 ? 1 : 0;
   if (g_stream_pf.load() && a->prefetch && a->prefetch_bytes >= 16) { p.pf = reinterpret_cast<const uint8_t*>(a->prefetch); p.pf_bytes = a->prefetch_bytes; }
 
   const int NB = a->batch > 8 ? 2 : 1;
   const int COLS = 8 * NB;
   // mirror of the kernel's shared-memory carve-up (assuming the dynamic window starts within the first 1 KB)
   const size_t stage = 2 * (size_t)kCW * (int4 ? 1088 : 576);
-  size_t off = 1024 + 128 + 128;
-  off += (size_t)kCW * 2 * 16 * COLS * 4 + kCW * 16 * 4 + 16 * 4;
-  if (int4) off += ((((size_t)a->batch * p.nkb) + 3) & ~(size_t)3) * 4;
-  off += (((size_t)a->batch * p.xstride * 2) + 127) & ~(size_t)127;
-  const size_t lut_at = (off + 0xFFFF) & ~(size_t)0xFFFF, ring_c = lut_at + 0x10000, end = 1024 + (size_t)kDynSmem;
-  const size_t slots = (lut_at - off) / stage + (ring_c < end ? (end - ring_c) / stage : 0);
-  if (ring_c > end || slots < 2) {
+  auto ring_slots = [&](int red_bufs) -> size_t {
+    size_t off = 1024 + 128 + 128;
+    off += (size_t)red_bufs * kCW * 2 * 16 * COLS * 4 + kCW * 16 * 4 + 16 * 4;
+    if (int4) off += ((((size_t)a->batch * p.nkb) + 3) & ~(size_t)3) * 4;
+    off += (((size_t)a->batch * p.xstride * 2) + 127) & ~(size_t)127;
+    const size_t lut_at = (off + 0xFFFF) & ~(size_t)0xFFFF, ring_c = lut_at + 0x10000, end = 1024 + (size_t)kDynSmem;
+    if (ring_c > end) return 0;
+    return (lut_at - off) / stage + (end - ring_c) / stage;
+  };
+  p.red_bufs = ring_slots(2) >= 3 ? 2 : 1;
+  if (ring_slots(p.red_bufs) < 2) {
     set_error("b200_qgemv_tiled: batch %d x K %lld does not fit the kernel's shared memory plan (activation rows need %zu bytes)",
               a->batch, (long long)a->K, (size_t)a->batch * p.xstride * 2);
     return B200_ERR_UNSUPPORTED;

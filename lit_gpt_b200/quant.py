@@ -188,9 +188,12 @@ class QLinear(nn.Module):
         shape is covered (and the activation fits its shared memory), else the reference-layout kernel.
         ``other``: the up-projection for the fused SwiGLU pair (this module being the gate)."""
         rows = x.numel() // self.in_features
-        if self.tiled is not None and (other is None or other.tiled is not None) and rows * (2 * self.in_features + 16) <= (64 if rows <= 8 else 48) * 1024:
-            return K.qgemv_tiled(x, self.tiled, self.out_features, self.in_features, self.quant_type, self.blocksize,
-                                 tiled2=None if other is None else other.tiled, prefetch=prefetch, **kw)
+        if self.tiled is not None and (other is None or other.tiled is not None) and rows * (2 * self.in_features + 16) <= 48 * 1024:
+            try:
+                return K.qgemv_tiled(x, self.tiled, self.out_features, self.in_features, self.quant_type, self.blocksize,
+                                     tiled2=None if other is None else other.tiled, prefetch=prefetch, **kw)
+            except NotImplementedError:  # shape outside the streaming kernel's shared-memory plan: nothing was launched
+                pass
         if other is not None:
             kw.update(packed2=other.weight.data, scale2=other.scale)
         kw.pop("bias2", None)
