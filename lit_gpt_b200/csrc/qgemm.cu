@@ -1,19 +1,292 @@
-// Prefill GEMM entry point.  The tcgen05/TMEM implementation lives in qgemm_tcgen05.cu once enabled; until then
-// this entry reports UNSUPPORTED so callers fail loudly instead of silently taking another path.
+// Prefill GEMM: y (M, N) = x (M, K) . dequant(W)^T on the 5th-generation tensor cores (tcgen05 + TMEM), DESIGN.md §5.4.
+//
+// Replaces, for T > 16 rows, bnb.nn.Linear4bit.forward's "dequantize_4bit of the WHOLE weight to bf16, then F.linear"
+// (call sites lit_gpt/model.py:519,619,656,713,714,716): the bf16 weight is never materialised in HBM.
+// Each CTA owns a (128 * MT tokens) x (128 output features) tile and walks K in blocks of 64:
+//   * 8 PRODUCER warps read the packed 4-bit weights (16 B = 32 codes per thread per k-block) and their absmax /
+//     {scale, zero}, rebuild the bf16 values with exactly the dequantise kernel's arithmetic
+//     (bf16_rn(code_fp32 * absmax_fp32), resp. bf16_rn(scale * (q - zero))) and write them, together with the
+//     activation tile, into shared memory in the tensor core's K-major 128-byte-swizzled layout;
+//   * ONE thread issues tcgen05.mma (cta_group::1, kind::f16, bf16 x bf16 -> fp32, M = 128, N = 128, K = 16) over
+//     shared-memory matrix descriptors; the fp32 accumulators live in TENSOR MEMORY (128 lanes x 128 columns per
+//     M sub-tile); tcgen05.commit hands each shared-memory stage back to the producers through an mbarrier;
+//   * 4 EPILOGUE warps (the first four producer warps, once K is exhausted) read the accumulators with tcgen05.ld
+//     (32 lanes x 32 columns per warp and instruction), add the bias, round to bf16 and store rows of y.
+// With MT = 2 one dequantised weight tile feeds 256 tokens, so the CUDA-core dequant (~500 clk per k-block) is
+// hidden under the tensor-core time (2 x 256 clk).
 #include "common.cuh"
+
+namespace b200 {
+
+struct GemmParams {
+  const uint8_t* packed;      // reference layout: nf4/fp4 bytes (N, K/2); int4 words (N, K/8)
+  const uint32_t* scale;      // fp32 absmax (N, K/64) or half2 {scale, zero} (N, K/128)
+  const __nv_bfloat16* x;     // (M, K)
+  const __nv_bfloat16* bias;  // (N) or null
+  __nv_bfloat16* y;           // (M, N)
+  int64_t M, N, K;
+  int qtype;
+};
+
+constexpr int kGProducers = 256;            // 8 warps
+constexpr int kGThreads = kGProducers + 32; // + the MMA / TMEM-allocator warp
+constexpr int kGStages = 4;
+constexpr int kBN = 128, kBK = 64;
+constexpr int kTileBytes = 128 * kBK * 2;   // one 128-row x 64-k bf16 operand tile = 16 KB
+
+__device__ __forceinline__ uint32_t g_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void g_mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void g_mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void g_mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  } while (!done);
+}
+
+// Shared-memory matrix descriptor, K-major operand, 128-byte swizzle (cute::UMMA::SmemDescriptor):
+//   [0,14) start address >> 4 | [16,30) leading byte offset >> 4 (unused for swizzled K-major: 1) |
+//   [32,46) stride byte offset >> 4 (8 rows x 128 B = 1024 B) | [46,48) version = 1 | [61,64) layout = 2 (SWIZZLE_128B)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): D = f32, A = B = bf16, both K-major, N = 128, M = 128
+constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(da), "l"(db), "r"(kIdesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {  // arrives on `bar` when all MMAs issued so far have completed
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// byte offset of the 16-byte chunk `c` (0..7) of row `r` inside a 128-row K-major SWIZZLE_128B tile
+__device__ __forceinline__ uint32_t sw128(int r, int c) { return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4)); }
+
+template <int MT>
+__global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmParams p) {
+  extern __shared__ __align__(1024) uint8_t g_smem[];
+  constexpr int STAGE = (MT + 1) * kTileBytes;      // MT activation tiles + 1 weight tile
+  constexpr int TMEM_COLS = 128 * MT;
+  __shared__ __align__(8) uint64_t s_bars[2 * kGStages + 1];
+  __shared__ uint32_t s_tmem;
+  __shared__ float s_code[16 * 32];                 // fp32 code book, one copy per lane (conflict-free look-ups)
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(g_smem) + 1023) & ~(uintptr_t)1023);
+  const uint32_t tiles_a = g_smem_u32(tiles);
+  const uint32_t full0 = g_smem_u32(&s_bars[0]), empty0 = g_smem_u32(&s_bars[kGStages]), done_bar = g_smem_u32(&s_bars[2 * kGStages]);
+  const int64_t n0 = (int64_t)blockIdx.x * kBN, m0 = (int64_t)blockIdx.y * (128 * MT);
+  const int nkb = (int)(p.K / kBK);
+  const bool int4 = p.qtype == B200_Q_INT4;
+
+  if (tid == 0) {
+    for (int s = 0; s < kGStages; ++s) { g_mbar_init(full0 + s * 8, kGProducers / 32); g_mbar_init(empty0 + s * 8, 1); }
+    g_mbar_init(done_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (!int4) {
+    for (int i = tid; i < 16 * 32; i += kGThreads) s_code[i] = code_value(p.qtype, i >> 5);
+  }
+  if (warp == kGProducers / 32) {  // the MMA warp also owns the tensor-memory allocation
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(g_smem_u32(&s_tmem)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = s_tmem;
+  griddep_launch();
+  griddep_wait();
+
+  if (warp < kGProducers / 32) {
+    // =========================================== PRODUCERS ======================================================
+    // weight tile: thread -> (row r = tid / 2, half h = tid % 2): 16 packed bytes = k [32h, 32h + 32) of the k-block
+    const int wr = tid >> 1, wh = tid & 1;
+    const int64_t wn = n0 + wr;
+    const bool wvalid = wn < p.N;
+    const uint8_t* wsrc = p.packed + (wvalid ? wn : 0) * (p.K >> 1) + wh * 16;
+    const uint32_t* ssrc = p.scale + (wvalid ? wn : 0) * (int4 ? (p.K >> 7) : (p.K >> 6));
+    for (int kb = 0; kb < nkb; ++kb) {
+      const int s = kb % kGStages;
+      if (kb >= kGStages) g_mbar_wait(empty0 + s * 8, ((kb / kGStages) - 1) & 1);
+      uint8_t* st = tiles + (size_t)s * STAGE;
+      // ---- activation tiles: 128 * MT rows x 8 chunks of 16 B, coalesced along K -----------------------------------
+#pragma unroll
+      for (int i = 0; i < (128 * MT * 8) / kGProducers; ++i) {
+        const int idx = i * kGProducers + tid, r = idx >> 3, c = idx & 7;
+        const int64_t m = m0 + r;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (m < p.M) v = *reinterpret_cast<const uint4*>(p.x + m * p.K + (int64_t)kb * kBK + c * 8);
+        *reinterpret_cast<uint4*>(st + (r >> 7) * kTileBytes + sw128(r & 127, c)) = v;
+      }
+      // ---- weight tile: dequantise 32 codes -> 4 chunks of 8 bf16 ----------------------------------------------------
+      uint4 q = make_uint4(0u, 0u, 0u, 0u);
+      uint32_t sc = 0u;
+      if (wvalid) {
+        q = ldg_stream_v4(wsrc + (int64_t)kb * 32);
+        sc = ssrc[int4 ? (kb >> 1) : kb];
+      }
+      const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
+      uint8_t* wt = st + MT * kTileBytes;
+      if (int4) {
+        const __half2 h2 = *reinterpret_cast<const __half2*>(&sc);
+        const float scale = __low2float(h2), zero = __high2float(h2);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {  // word j = k [32h + 8j, +8), element e in bits 4e
+          uint32_t o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float a = scale * ((float)((qw[j] >> (8 * e)) & 15u) - zero);
+            const float b = scale * ((float)((qw[j] >> (8 * e + 4)) & 15u) - zero);
+            o[e] = pack_bf16(a, b);
+          }
+          *reinterpret_cast<uint4*>(wt + sw128(wr, wh * 4 + j)) = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+      } else {
+        const float am = __uint_as_float(sc);
+        const float* code = s_code + lane;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {  // word j = bytes 4j..4j+3 = k [32h + 8j, +8); even element in the HIGH nibble
+          uint32_t o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t byte = (qw[j] >> (8 * e)) & 255u;
+            o[e] = pack_bf16(code[(byte >> 4) * 32] * am, code[(byte & 15u) * 32] * am);
+          }
+          *reinterpret_cast<uint4*>(wt + sw128(wr, wh * 4 + j)) = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core
+      __syncwarp();
+      if (lane == 0) g_mbar_arrive(full0 + s * 8);
+    }
+  } else if (lane == 0) {
+    // =========================================== MMA ISSUER =====================================================
+    for (int kb = 0; kb < nkb; ++kb) {
+      const int s = kb % kGStages;
+      g_mbar_wait(full0 + s * 8, (kb / kGStages) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t sa = tiles_a + s * STAGE;
+      const uint64_t db = umma_desc_sw128(sa + MT * kTileBytes);
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+        const uint64_t da = umma_desc_sw128(sa + mt * kTileBytes);
+#pragma unroll
+        for (int k = 0; k < kBK / 16; ++k)  // +32 B along K inside the swizzle atom = +2 in the address field
+          umma_bf16(tmem + mt * 128, da + 2 * k, db + 2 * k, (kb | k) != 0);
+      }
+      umma_commit(empty0 + s * 8);   // stage reusable once these MMAs have read it (implies fence::before_thread_sync)
+    }
+    umma_commit(done_bar);           // accumulators complete
+  }
+
+  // =============================================== EPILOGUE =======================================================
+  if (warp < 4) {
+    g_mbar_wait(done_bar, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+    for (int mt = 0; mt < MT; ++mt) {
+      const int64_t m = m0 + mt * 128 + warp * 32 + lane;        // this thread's output row (TMEM lane = row)
+#pragma unroll 1
+      for (int c0 = 0; c0 < kBN; c0 += 32) {
+        uint32_t v[32];
+        const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(mt * 128 + c0);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,"
+            "%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+              "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+              "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+              "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+            : "r"(taddr));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (m < p.M) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            const int64_t n = n0 + c0 + j;
+            if (n < p.N) {  // N % 8 == 0 (host check): a chunk is either fully inside or fully outside
+              uint32_t o[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float a = __uint_as_float(v[j + 2 * e]), b = __uint_as_float(v[j + 2 * e + 1]);
+                if (p.bias) { a += __bfloat162float(p.bias[n + 2 * e]); b += __bfloat162float(p.bias[n + 2 * e + 1]); }
+                o[e] = pack_bf16(a, b);
+              }
+              *reinterpret_cast<uint4*>(p.y + m * p.N + n) = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+          }
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == kGProducers / 32) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
+  }
+}
+
+template <int MT>
+static cudaError_t launch_gemm(const GemmParams& p, cudaStream_t st) {
+  constexpr int smem = kGStages * (MT + 1) * kTileBytes + 1024;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(qgemm_tcgen05_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  dim3 grid((unsigned)((p.N + kBN - 1) / kBN), (unsigned)((p.M + 128 * MT - 1) / (128 * MT)));
+  return launch(qgemm_tcgen05_kernel<MT>, grid, dim3(kGThreads), (size_t)smem, st, p);
+}
+
+}  // namespace b200
+
+using namespace b200;
 
 extern "C" {
 
 size_t b200_qgemm_workspace_bytes(int64_t M, int64_t N, int64_t K) {
   (void)M; (void)N; (void)K;
-  return 0;
+  return 0;  // accumulators live in tensor memory; nothing is staged in HBM
 }
 
 int b200_qgemm(const b200_qgemm_args* a, b200_stream_t stream) {
-  (void)stream;
   B200_CHECK_ARG(a != nullptr, "b200_qgemm: null args");
-  b200::set_error("b200_qgemm: tcgen05 prefill GEMM not built into this library yet");
-  return B200_ERR_UNSUPPORTED;
+  B200_CHECK_ARG(a->packed && a->scale && a->x && a->y, "b200_qgemm: null packed/scale/x/y pointer");
+  B200_CHECK_ARG(a->M > 0 && a->N > 0 && a->K > 0, "b200_qgemm: M, N, K must be positive");
+  B200_CHECK_ARG(a->qtype == B200_Q_NF4 || a->qtype == B200_Q_FP4 || a->qtype == B200_Q_INT4, "b200_qgemm: bad qtype %d", a->qtype);
+  const bool int4 = a->qtype == B200_Q_INT4;
+  if (a->blocksize != (int4 ? 128 : 64) || a->K % (int4 ? 128 : 64) != 0 || a->N % 8 != 0) {
+    set_error("b200_qgemm: needs blocksize %d, K %% %d == 0 and N %% 8 == 0 (blocksize=%d N=%lld K=%lld)", int4 ? 128 : 64, int4 ? 128 : 64,
+              a->blocksize, (long long)a->N, (long long)a->K);
+    return B200_ERR_UNSUPPORTED;
+  }
+  B200_CHECK_ARG(a->N <= 65535LL * kBN && a->M <= 65535LL * 128, "b200_qgemm: shape too large for the grid");
+  B200_CHECK_ARG(((reinterpret_cast<uintptr_t>(a->packed) | reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(a->y)) & 15) == 0,
+                 "b200_qgemm: packed / x / y must be 16-byte aligned");
+  GemmParams p{};
+  p.packed = reinterpret_cast<const uint8_t*>(a->packed);
+  p.scale = reinterpret_cast<const uint32_t*>(a->scale);
+  p.x = reinterpret_cast<const __nv_bfloat16*>(a->x);
+  p.bias = reinterpret_cast<const __nv_bfloat16*>(a->bias);
+  p.y = reinterpret_cast<__nv_bfloat16*>(a->y);
+  p.M = a->M; p.N = a->N; p.K = a->K; p.qtype = a->qtype;
+  cudaStream_t st = (cudaStream_t)stream;
+  const cudaError_t e = a->M > 128 ? launch_gemm<2>(p, st) : launch_gemm<1>(p, st);
+  if (e != cudaSuccess) {
+    set_error("b200_qgemm: launch failed: %s", cudaGetErrorString(e));
+    return B200_ERR_CUDA;
+  }
+  return B200_OK;
 }
 
 }  // extern "C"

@@ -187,6 +187,23 @@ def qgemv_tiled_tune(depth: int = 0, ctas_per_sm: int = 0, l2_prefetch: bool = T
 # ---------------------------------------------------------------------------------------------------------
 # norm / embedding / argmax
 # ---------------------------------------------------------------------------------------------------------
+def qgemm(x: torch.Tensor, packed: torch.Tensor, scale: torch.Tensor, N: int, K: int, quant_type: str = "nf4", blocksize: int = 64,
+          bias: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Prefill GEMM y (M, N) = x (M, K) . dequant(W)^T on tcgen05 / TMEM (reference-layout packed weights + scales).
+    Raises NotImplementedError for shapes the kernel does not cover (K not a multiple of the block, N % 8 != 0)."""
+    C.require_cuda(x, packed, scale, bias)
+    x = _bf16c(x, "x")
+    bias = _bf16c(bias, "bias")
+    M = x.numel() // K
+    if x.numel() != M * K:
+        raise C.B200Error("qgemm: x does not hold whole rows of length K")
+    y = out if out is not None else torch.empty(tuple(x.shape[:-1]) + (N,), dtype=torch.bfloat16, device=x.device)
+    args = C.QGemmArgs(packed=packed.data_ptr(), scale=scale.data_ptr(), qtype=QTYPES[quant_type], blocksize=blocksize, M=M, N=N, K=K,
+                       x=x.data_ptr(), bias=C.ptr(bias), y=y.data_ptr(), workspace=None, workspace_bytes=0)
+    C.check(C.load().b200_qgemm(ctypes.byref(args), C.stream_ptr(x.device)), "qgemm")
+    return y
+
+
 def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float = 1e-5, delta: Optional[torch.Tensor] = None,
             sum_out: Optional[torch.Tensor] = None) -> torch.Tensor:
     C.require_cuda(x, weight)

@@ -205,9 +205,15 @@ class QLinear(nn.Module):
 
 
 def prefill_linear(q: QLinear, x: torch.Tensor) -> torch.Tensor:
-    """T > 16 rows: dense contraction.  Uses the library's prefill GEMM when it supports the shape; until the
-    tcgen05 kernel lands this is the reference's own formulation (dequantize_4bit to bf16, then a library GEMM,
-    SURVEY Q1) with the dequantisation done by this library's kernel."""
+    """T > 16 rows: the tcgen05 / TMEM dequant-GEMM (csrc/qgemm.cu): weights are dequantised tile by tile in shared
+    memory, the bf16 matrix never exists in HBM.  Shapes it does not cover (K not a multiple of the quantisation
+    block, N % 8 != 0: toy configs only) take the reference's own formulation -- dequantize_4bit to bf16, then a
+    library GEMM -- with the dequantisation done by this library's kernel."""
+    if x.dtype == torch.bfloat16:
+        try:
+            return K.qgemm(x, q.weight.data, q.scale, q.out_features, q.in_features, q.quant_type, q.blocksize, bias=q.bias)
+        except NotImplementedError:
+            pass
     w = q.dequantize(torch.bfloat16)
     return F.linear(x, w, q.bias)
 

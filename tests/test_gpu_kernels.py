@@ -417,3 +417,40 @@ def test_qgemv_tiled_onehot_reads_dequantised_column(K):
     col = K.qgemv_tiled(onehot, tiled, N, Kdim)
     deq = K.dequantize_4bit(packed, absmax, (N, Kdim), torch.float32)
     assert (col[0].float() - deq[:, 1234]).abs().max() <= 2 ** -8 * deq[:, 1234].abs().max()
+
+
+# ---- prefill GEMM on tcgen05 / TMEM (csrc/qgemm.cu) ---------------------------------------------------------------
+@pytest.mark.parametrize("qt", ["nf4", "fp4", "int4"])
+@pytest.mark.parametrize("M,N,Kdim", [(128, 128, 128), (17, 8, 128), (256, 256, 512), (300, 520, 1024), (129, 4096, 4096), (1000, 344, 11008)])
+def test_qgemm_tcgen05(K, qt, M, N, Kdim):
+    w, _, packed, scale, bs, deq = _gemv_case(K, N, Kdim, 1, qt, seed=M + N)
+    x = _randw((M, Kdim), 5, std=1.0)
+    bias = _randw((N,), 6, std=0.5) if M == 300 else None
+    y = K.qgemm(x.cuda(), packed, scale, N, Kdim, qt, bs, bias=None if bias is None else bias.cuda())
+    assert y.shape == (M, N)
+    # the weight tile the tensor core sees is bf16_rn(dequant): same operands as the reference's dequantize + F.linear,
+    # so the only difference to a library GEMM on those operands is the fp32 accumulation order
+    wb = deq.to(torch.bfloat16)
+    ref = torch.nn.functional.linear(x.cuda(), wb.cuda(), None if bias is None else bias.cuda()).float().cpu()
+    wide = x.double() @ wb.double().T + (0 if bias is None else bias.double())
+    e_k = (y.float().cpu().double() - wide).abs().max().item()
+    e_t = (ref.double() - wide).abs().max().item()
+    scale_y = wide.abs().max().item()
+    assert e_k <= 2.0 * e_t + 2 ** -8 * scale_y, f"kernel err {e_k:.4g} vs library-GEMM err {e_t:.4g} (|y|max {scale_y:.3g})"
+
+
+def test_qgemm_onehot_rows_read_dequantised_weights(K):
+    """x = identity block: y must be EXACTLY bf16(dequant(W)) -- checks the swizzled operand layout, the code book,
+    the nibble order and the TMEM read-back mapping without any accumulation error."""
+    N, Kdim = 136, 256
+    for qt in ("nf4", "int4"):
+        w, _, packed, scale, bs, deq = _gemv_case(K, N, Kdim, 1, qt, seed=3)
+        x = torch.eye(Kdim, dtype=torch.bfloat16)
+        y = K.qgemm(x.cuda(), packed, scale, N, Kdim, qt, bs)
+        assert torch.equal(y.cpu(), deq.to(torch.bfloat16).T.contiguous()), qt
+
+
+def test_qgemm_unsupported_shapes(K):
+    w, _, packed, scale, bs, _ = _gemv_case(K, 20, 96, 1, "nf4")
+    with pytest.raises(NotImplementedError):
+        K.qgemm(torch.zeros(32, 96, dtype=torch.bfloat16, device="cuda"), packed, scale, 20, 96, "nf4", 64)
