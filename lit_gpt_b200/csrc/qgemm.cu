@@ -3,7 +3,7 @@
 // Replaces, for T > 16 rows, bnb.nn.Linear4bit.forward's "dequantize_4bit of the WHOLE weight to bf16, then F.linear"
 // (call sites lit_gpt/model.py:519,619,656,713,714,716): the bf16 weight is never materialised in HBM.
 // Each CTA owns a (128 * MT tokens) x (128 output features) tile and walks K in blocks of 64:
-//   * 8 PRODUCER warps read the packed 4-bit weights (16 B = 32 codes per thread per k-block) and their absmax /
+//   * 16 PRODUCER warps read the packed 4-bit weights (8 B = 16 codes per thread per k-block) and their absmax /
 //     {scale, zero}, rebuild the bf16 values with exactly the dequantise kernel's arithmetic
 //     (bf16_rn(code_fp32 * absmax_fp32), resp. bf16_rn(scale * (q - zero))) and write them, together with the
 //     activation tile, into shared memory in the tensor core's K-major 128-byte-swizzled layout;
@@ -28,7 +28,7 @@ struct GemmParams {
   int qtype;
 };
 
-constexpr int kGProducers = 256;            // 8 warps
+constexpr int kGProducers = 512;            // 16 warps: 4 per scheduler, enough to hide the look-up latency
 constexpr int kGThreads = kGProducers + 32; // + the MMA / TMEM-allocator warp
 constexpr int kGStages = 4;
 constexpr int kBN = 128, kBK = 64;
@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
   const bool int4 = p.qtype == B200_Q_INT4;
 
   if (tid == 0) {
-    for (int s = 0; s < kGStages; ++s) { g_mbar_init(full0 + s * 8, kGProducers / 32); g_mbar_init(empty0 + s * 8, 1); }
+    for (int s = 0; s < kGStages; ++s) { g_mbar_init(full0 + s * 8, 2 * (kGProducers / 32)); g_mbar_init(empty0 + s * 8, 1); }
     g_mbar_init(done_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -109,39 +109,66 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
 
   if (warp < kGProducers / 32) {
     // =========================================== PRODUCERS ======================================================
-    // weight tile: thread -> (row r = tid / 2, half h = tid % 2): 16 packed bytes = k [32h, 32h + 32) of the k-block
-    const int wr = tid >> 1, wh = tid & 1;
+    // Software pipeline per thread: the activation tile of k-block kb is fetched with cp.async (16 B, zero-filled past
+    // M) straight into its swizzled slot and only waited for kALag iterations later; the packed weights and scales are
+    // prefetched into registers kWLag k-blocks ahead.  full[s] therefore collects TWO arrivals per warp and phase: one
+    // for the dequantised weight tile (iteration kb), one for the activation tile (iteration kb + kALag).
+    constexpr int kALag = 2, kWLag = 2;
+    // weight tile: thread -> (row r = tid / 4, quarter h = tid % 4): 8 packed bytes = k [16h, 16h + 16) of the k-block
+    const int wr = tid >> 2, wh = tid & 3;
     const int64_t wn = n0 + wr;
     const bool wvalid = wn < p.N;
-    const uint8_t* wsrc = p.packed + (wvalid ? wn : 0) * (p.K >> 1) + wh * 16;
+    const uint8_t* wsrc = p.packed + (wvalid ? wn : 0) * (p.K >> 1) + wh * 8;
     const uint32_t* ssrc = p.scale + (wvalid ? wn : 0) * (int4 ? (p.K >> 7) : (p.K >> 6));
+    uint2 qn[kWLag];
+    uint32_t scn[kWLag];
+#pragma unroll
+    for (int i = 0; i < kWLag; ++i) {
+      qn[i] = make_uint2(0u, 0u);
+      scn[i] = 0u;
+      if (wvalid && i < nkb) { qn[i] = ldg_stream_v2(wsrc + (int64_t)i * 32); scn[i] = ssrc[int4 ? (i >> 1) : i]; }
+    }
+    // activation chunks of this thread: rows r_i = (i * 512 + tid) / 8, chunk c = tid % 8 (fixed); source pointers and
+    // swizzled destinations are loop-invariant up to the k-block / stage offset
+    constexpr int ACH = (128 * MT * 8) / kGProducers;
+    const int ac = tid & 7;
+    const __nv_bfloat16* asrc[ACH];
+    uint32_t adst[ACH], asz[ACH];
+#pragma unroll
+    for (int i = 0; i < ACH; ++i) {
+      const int r = (i * kGProducers + tid) >> 3;
+      const int64_t m = m0 + r;
+      asz[i] = m < p.M ? 16u : 0u;
+      asrc[i] = p.x + (m < p.M ? m : 0) * p.K + ac * 8;
+      adst[i] = tiles_a + (uint32_t)((r >> 7) * kTileBytes) + sw128(r & 127, ac);
+    }
+    const uint32_t wdst0 = (uint32_t)(MT * kTileBytes) + sw128(wr, wh * 2), wdst1 = (uint32_t)(MT * kTileBytes) + sw128(wr, wh * 2 + 1);
     for (int kb = 0; kb < nkb; ++kb) {
       const int s = kb % kGStages;
       if (kb >= kGStages) g_mbar_wait(empty0 + s * 8, ((kb / kGStages) - 1) & 1);
       uint8_t* st = tiles + (size_t)s * STAGE;
-      // ---- activation tiles: 128 * MT rows x 8 chunks of 16 B, coalesced along K -----------------------------------
+      // ---- activation tiles: 128 * MT rows x 8 chunks of 16 B, coalesced along K, asynchronous ----------------------
 #pragma unroll
-      for (int i = 0; i < (128 * MT * 8) / kGProducers; ++i) {
-        const int idx = i * kGProducers + tid, r = idx >> 3, c = idx & 7;
-        const int64_t m = m0 + r;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (m < p.M) v = *reinterpret_cast<const uint4*>(p.x + m * p.K + (int64_t)kb * kBK + c * 8);
-        *reinterpret_cast<uint4*>(st + (r >> 7) * kTileBytes + sw128(r & 127, c)) = v;
+      for (int i = 0; i < ACH; ++i)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(adst[i] + (uint32_t)(s * STAGE)), "l"(asrc[i] + (int64_t)kb * kBK), "r"(asz[i]) : "memory");
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      // ---- weight tile: dequantise 16 codes -> 2 chunks of 8 bf16 ----------------------------------------------------
+      const uint2 q = qn[0];
+      const uint32_t sc = scn[0];
+#pragma unroll
+      for (int i = 0; i + 1 < kWLag; ++i) { qn[i] = qn[i + 1]; scn[i] = scn[i + 1]; }
+      {
+        const int kn = kb + kWLag;
+        qn[kWLag - 1] = make_uint2(0u, 0u);
+        scn[kWLag - 1] = 0u;
+        if (wvalid && kn < nkb) { qn[kWLag - 1] = ldg_stream_v2(wsrc + (int64_t)kn * 32); scn[kWLag - 1] = ssrc[int4 ? (kn >> 1) : kn]; }
       }
-      // ---- weight tile: dequantise 32 codes -> 4 chunks of 8 bf16 ----------------------------------------------------
-      uint4 q = make_uint4(0u, 0u, 0u, 0u);
-      uint32_t sc = 0u;
-      if (wvalid) {
-        q = ldg_stream_v4(wsrc + (int64_t)kb * 32);
-        sc = ssrc[int4 ? (kb >> 1) : kb];
-      }
-      const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
-      uint8_t* wt = st + MT * kTileBytes;
+      const uint32_t qw[2] = {q.x, q.y};
       if (int4) {
         const __half2 h2 = *reinterpret_cast<const __half2*>(&sc);
         const float scale = __low2float(h2), zero = __high2float(h2);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {  // word j = k [32h + 8j, +8), element e in bits 4e
+        for (int j = 0; j < 2; ++j) {  // word j = k [16h + 8j, +8), element e in bits 4e
           uint32_t o[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
@@ -149,25 +176,35 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
             const float b = scale * ((float)((qw[j] >> (8 * e + 4)) & 15u) - zero);
             o[e] = pack_bf16(a, b);
           }
-          *reinterpret_cast<uint4*>(wt + sw128(wr, wh * 4 + j)) = make_uint4(o[0], o[1], o[2], o[3]);
+          *reinterpret_cast<uint4*>(st + (j ? wdst1 : wdst0)) = make_uint4(o[0], o[1], o[2], o[3]);
         }
       } else {
         const float am = __uint_as_float(sc);
         const float* code = s_code + lane;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {  // word j = bytes 4j..4j+3 = k [32h + 8j, +8); even element in the HIGH nibble
+        for (int j = 0; j < 2; ++j) {  // word j = bytes 4j..4j+3 = k [16h + 8j, +8); even element in the HIGH nibble
           uint32_t o[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const uint32_t byte = (qw[j] >> (8 * e)) & 255u;
             o[e] = pack_bf16(code[(byte >> 4) * 32] * am, code[(byte & 15u) * 32] * am);
           }
-          *reinterpret_cast<uint4*>(wt + sw128(wr, wh * 4 + j)) = make_uint4(o[0], o[1], o[2], o[3]);
+          *reinterpret_cast<uint4*>(st + (j ? wdst1 : wdst0)) = make_uint4(o[0], o[1], o[2], o[3]);
         }
       }
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core
+      asm volatile("cp.async.wait_group %0;" ::"n"(kALag) : "memory");   // this thread's activation chunks of kb - kALag landed
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // generic-proxy writes -> visible to the tensor core
       __syncwarp();
-      if (lane == 0) g_mbar_arrive(full0 + s * 8);
+      if (lane == 0) {
+        g_mbar_arrive(full0 + s * 8);                                                    // weight tile of kb
+        if (kb >= kALag) g_mbar_arrive(full0 + ((kb - kALag) % kGStages) * 8);           // activation tiles of kb - kALag
+      }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    if (lane == 0) {
+      for (int kb = nkb > kALag ? nkb - kALag : 0; kb < nkb; ++kb) g_mbar_arrive(full0 + (kb % kGStages) * 8);
     }
   } else if (lane == 0) {
     // =========================================== MMA ISSUER =====================================================
