@@ -386,7 +386,15 @@ def main() -> None:
     import torch.distributed as dist
 
     if dist.is_available() and dist.is_initialized():
-        dist.destroy_process_group()
+        # CUDA graphs that captured NCCL all-reduces keep the communicator busy at teardown (destroy_process_group and
+        # interpreter exit both hang): everything is printed and flushed, so leave without running destructors.
+        import torch
+
+        torch.cuda.synchronize()
+        dist.barrier()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
