@@ -96,23 +96,52 @@ __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<H
   const bool last_split = split == p.nsplit - 1;
 
   // ---- q (and, in the last split, the new k / v): load, RoPE, keep as bf16-exact floats in smem -----------
+  // All global loads of this phase are issued together (q heads, k, v next to the position load above) and the
+  // cos / sin entries are fetched once per thread, so the phase costs two dependent memory round trips and two
+  // barriers regardless of the number of heads.  The raw vectors are staged in s_acc, unused until the final merge.
   const __nv_bfloat16* grp = p.qkv + ((int64_t)b * p.n_groups + gi) * (p.qpk + 2) * HS;
-  for (int h = 0; h < nh; ++h) {
-    for (int d = tid; d < HS; d += 128) s_tmp[d] = ld_act_bf16(grp + (h0 + h) * HS + d);
-    sync();
-    for (int d = tid; d < HS; d += 128) s_q[h][d] = rope_elem(s_tmp, d, p.rope_n, p.cos, p.sin, p.table_bf16, p.table_presel ? 0 : pos);
-    sync();
+  float (&raw_q)[QPK][HS] = s_acc[0];
+  float* raw_k = s_acc[1][0];
+  if (tid < HS) {
+    float rq[QPK], rk = 0.f, rv = 0.f;
+#pragma unroll
+    for (int h = 0; h < QPK; ++h) rq[h] = h < nh ? ld_act_bf16(grp + (h0 + h) * HS + tid) : 0.f;
+    if (last_split) { rk = ld_act_bf16(grp + p.qpk * HS + tid); rv = ld_act_bf16(grp + (p.qpk + 1) * HS + tid); }
+#pragma unroll
+    for (int h = 0; h < QPK; ++h) raw_q[h][tid] = rq[h];
+    raw_k[tid] = rk;
+    s_v[tid] = rv;
   }
-  if (last_split) {
-    for (int d = tid; d < HS; d += 128) { s_tmp[d] = ld_act_bf16(grp + p.qpk * HS + d); s_v[d] = ld_act_bf16(grp + (p.qpk + 1) * HS + d); }
-    sync();
-    for (int d = tid; d < HS; d += 128) s_k[d] = rope_elem(s_tmp, d, p.rope_n, p.cos, p.sin, p.table_bf16, p.table_presel ? 0 : pos);
-    sync();
-    if (hc == 0) {  // exactly one CTA per (batch, group) appends to the cache (KVCache.forward, model.py:793-794)
-      const int64_t off = (((int64_t)b * p.n_groups + gi) * p.max_seq + pos) * HS;
-      for (int d = tid; d < HS; d += 128) { p.kc[off + d] = __float2bfloat16_rn(s_k[d]); p.vc[off + d] = __float2bfloat16_rn(s_v[d]); }
+  sync();
+  if (tid < HS) {
+    const int d = tid, n = p.rope_n, half = n >> 1;
+    float c = 1.f, sn = 0.f;
+    if (d < n) {
+      const int64_t row = p.table_presel ? 0 : pos;
+      c = table_at(p.cos, p.table_bf16, row * n + d);
+      sn = table_at(p.sin, p.table_bf16, row * n + d);
+    }
+    // apply_rope (lit_gpt/model.py:767-773), same rounding points as rope_elem()
+    auto rope = [&](const float* x) -> float {
+      if (d >= n) return x[d];
+      const float rot = d < half ? -x[d + half] : x[d - half];
+      if (p.table_bf16) return round_bf16(__fadd_rn(round_bf16(__fmul_rn(x[d], c)), round_bf16(__fmul_rn(rot, sn))));
+      return round_bf16(__fadd_rn(__fmul_rn(x[d], c), __fmul_rn(rot, sn)));
+    };
+#pragma unroll
+    for (int h = 0; h < QPK; ++h)
+      if (h < nh) s_q[h][d] = rope(raw_q[h]);
+    if (last_split) {
+      const float kd = rope(raw_k);
+      s_k[d] = kd;
+      if (hc == 0) {  // exactly one CTA per (batch, group) appends to the cache (KVCache.forward, model.py:793-794)
+        const int64_t off = (((int64_t)b * p.n_groups + gi) * p.max_seq + pos) * HS;
+        p.kc[off + d] = __float2bfloat16_rn(kd);
+        p.vc[off + d] = __float2bfloat16_rn(s_v[d]);
+      }
     }
   }
+  sync();
 
   const int gidx = lane / LPK, dl = lane % LPK;
   float q[QPK][DPL];
@@ -157,16 +186,22 @@ __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<H
   const int64_t kbeg = (int64_t)split * per, kend = min(pos, kbeg + per);
   const __nv_bfloat16* kbase = p.kc + ((int64_t)b * p.n_groups + gi) * p.max_seq * HS + dl * DPL;
   const __nv_bfloat16* vbase = p.vc + ((int64_t)b * p.n_groups + gi) * p.max_seq * HS + dl * DPL;
-  for (int64_t base = kbeg + warp * GPW; base < kend; base += 2 * SLOTS) {  // warp-uniform trip count
-    const int64_t ka = base + gidx, kb = ka + SLOTS;
-    const bool va = ka < kend, vb = kb < kend;
-    uint32_t kra[NR], vra[NR], krb[NR], vrb[NR];
+  constexpr int KPI = 4;  // keys per lane group and iteration: all their K / V rows are in flight before the first update
+  for (int64_t base = kbeg + warp * GPW; base < kend; base += KPI * SLOTS) {  // warp-uniform trip count
+    uint32_t kr[KPI][NR], vr[KPI][NR];
+    bool ok[KPI];
 #pragma unroll
-    for (int i = 0; i < NR; ++i) kra[i] = vra[i] = krb[i] = vrb[i] = 0u;
-    if (va) { load_row<NR>(kra, kbase + ka * HS); load_row<NR>(vra, vbase + ka * HS); }
-    if (vb) { load_row<NR>(krb, kbase + kb * HS); load_row<NR>(vrb, vbase + kb * HS); }
-    update(kra, vra, va);
-    if (base + SLOTS < kend) update(krb, vrb, vb);
+    for (int u = 0; u < KPI; ++u) {
+      const int64_t kk = base + gidx + (int64_t)u * SLOTS;
+      ok[u] = kk < kend;
+#pragma unroll
+      for (int i = 0; i < NR; ++i) kr[u][i] = vr[u][i] = 0u;
+      if (ok[u]) { load_row<NR>(kr[u], kbase + kk * HS); load_row<NR>(vr[u], vbase + kk * HS); }
+    }
+#pragma unroll
+    for (int u = 0; u < KPI; ++u) {
+      if (base + (int64_t)u * SLOTS < kend) update(kr[u], vr[u], ok[u]);  // warp-uniform condition (shuffles inside)
+    }
   }
   // ---- the key being appended comes from shared memory (never re-read from HBM) ---------------------------
   if (last_split && warp == 0) {

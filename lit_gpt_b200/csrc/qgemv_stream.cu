@@ -211,12 +211,22 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     else { lo = code_value(p.qtype, e >> 4); hi = code_value(p.qtype, e & 15); }   // even element = HIGH nibble
     lut[e * 64 + l] = pack_bf16(lo, hi);
   }
+  // RMSNorm weights are constants: fetch this thread's first chunks BEFORE waiting for the previous kernel, so their
+  // global-load latency is off the critical path between the two kernels
+  const int chunks = (int)(p.K >> 3);
+  uint4 nwreg[3] = {make_uint4(0u, 0u, 0u, 0u), make_uint4(0u, 0u, 0u, 0u), make_uint4(0u, 0u, 0u, 0u)};
+  if (p.norm_w) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int c = tid + i * kConsumers;
+      if (c < chunks) nwreg[i] = *reinterpret_cast<const uint4*>(p.norm_w + c * 8);
+    }
+  }
   griddep_launch();
   griddep_wait();
 
   // ---- activation prologue: (x + delta) -> optional RMSNorm -> bf16 rows in shared memory ---------------------
   const bool designated = blockIdx.x == 0;
-  const int chunks = (int)(p.K >> 3);
   for (int b = 0; b < B; ++b) {
     float ss = 0.f;
     for (int c = tid; c < chunks; c += kConsumers) {
@@ -250,9 +260,10 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
     for (int b = 0; b < B; ++b) {
       const float rstd = s_rstd[b];
-      for (int c = tid; c < chunks; c += kConsumers) {  // same thread owns the same chunk as above
+      int ci = 0;
+      for (int c = tid; c < chunks; c += kConsumers, ++ci) {  // same thread owns the same chunk as above
         uint4 v = *reinterpret_cast<uint4*>(x_s + b * p.xstride + c * 8);
-        const uint4 nw = *reinterpret_cast<const uint4*>(p.norm_w + c * 8);
+        const uint4 nw = ci == 0 ? nwreg[0] : ci == 1 ? nwreg[1] : ci == 2 ? nwreg[2] : *reinterpret_cast<const uint4*>(p.norm_w + c * 8);
         // weight * (x * rstd), fp32, one cast (rmsnorm.py:24-25)
         v.x = pack_bf16(bf16lo(nw.x) * (bf16lo(v.x) * rstd), bf16hi(nw.x) * (bf16hi(v.x) * rstd));
         v.y = pack_bf16(bf16lo(nw.y) * (bf16lo(v.y) * rstd), bf16hi(nw.y) * (bf16hi(v.y) * rstd));
@@ -467,7 +478,7 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   }
 }
 
-static std::atomic<int> g_stream_depth{0}, g_stream_occ{0}, g_stream_pf{1};
+static std::atomic<int> g_stream_depth{0}, g_stream_occ{0}, g_stream_pf{0};  // L2 prefetch of the next launch's weights: off by default (no measured gain, extra DRAM traffic when lines are evicted before use)
 
 template <int NB, bool INT4>
 static cudaError_t launch_stream(const StreamParams& p, int gx, cudaStream_t st) {
