@@ -111,8 +111,9 @@ __global__ void __launch_bounds__(kDThreadsAll, 1) decode_step_kernel(const Step
   const uint32_t xsum_a = off;          off += INT4 ? (((uint32_t)(sp.batch * (sp.max_k >> 6)) + 3u) & ~3u) * 4 : 0;
   const uint32_t xs_a = off;            off += (((uint32_t)sp.batch * sp.xstride * 2) + 127u) & ~127u;
   const uint32_t ringA_a = off;
-  const uint32_t lut_a = (off + 0xFFFFu) & ~0xFFFFu;                                    // 64 KB aligned
-  const uint32_t ringC_a = lut_a + 0x10000u;
+  // int4 dequantises arithmetically: no table, the whole remainder is ring
+  const uint32_t lut_a = INT4 ? off : (off + 0xFFFFu) & ~0xFFFFu;                       // 64 KB aligned
+  const uint32_t ringC_a = INT4 ? off : lut_a + 0x10000u;
   const uint32_t end_a = b0 + kDDynSmem;
   const int nA = (int)((lut_a - ringA_a) / STAGE);
   const int nC = ringC_a < end_a ? (int)((end_a - ringC_a) / STAGE) : 0;
@@ -197,10 +198,10 @@ __global__ void __launch_bounds__(kDThreadsAll, 1) decode_step_kernel(const Step
     return;
   }
   // ================================== CONSUMER WARPS ===============================================================
-  for (int i = tid; i < 256 * 32; i += kDConsumers) {
+  for (int i = tid; i < (INT4 ? 0 : 256 * 32); i += kDConsumers) {
     const int e = i >> 5, l = i & 31;
     float lo, hi;
-    if (INT4) { lo = (float)(e & 15); hi = (float)(e >> 4); }                      // k even = LOW nibble
+    if (INT4) { lo = (float)(e & 15); hi = (float)(e >> 4); }                      // (unused: int4 has no table)
     else { lo = code_value(sp.qtype, e >> 4); hi = code_value(sp.qtype, e & 15); } // even element = HIGH nibble
     lut[e * 64 + l] = pack_bf16(lo, hi);
   }
@@ -363,6 +364,19 @@ __global__ void __launch_bounds__(kDThreadsAll, 1) decode_step_kernel(const Step
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
+          if constexpr (INT4) {
+            // no table: the tiled words hold even codes in the low and odd codes in the high half-word, so one shift +
+            // one LOP3 yields the bf16 pair (128 + e_2p, 128 + e_2p+1); the +128 joins the zero-point term below
+            const int sh = 8 * (j & 1);
+            const uint32_t ua = (j < 2) ? w0.x : w0.y, ub = (j < 2) ? w0.z : w0.w, va = (j < 2) ? w1.x : w1.y, vb = (j < 2) ? w1.z : w1.w;
+            const uint32_t m = 0x000F000Fu, c = 0x43004300u;
+#pragma unroll
+            for (int nb = 0; nb < NB; ++nb) {
+              mma16816(p0[nb], ((ua >> sh) & m) | c, ((ub >> sh) & m) | c, ((ua >> (sh + 4)) & m) | c, ((ub >> (sh + 4)) & m) | c, xb[nb][2 * j], xb[nb][2 * j + 1]);
+              mma16816(p1[nb], ((va >> sh) & m) | c, ((vb >> sh) & m) | c, ((va >> (sh + 4)) & m) | c, ((vb >> (sh + 4)) & m) | c, xb[nb][2 * j], xb[nb][2 * j + 1]);
+            }
+            continue;
+          }
           const uint32_t sel0 = (j & 1) ? 0x7624u : 0x7604u, sel1 = (j & 1) ? 0x7634u : 0x7614u;
           {
             const uint32_t wa = (j < 2) ? w0.x : w0.y, wb = (j < 2) ? w0.z : w0.w;
@@ -380,8 +394,8 @@ __global__ void __launch_bounds__(kDThreadsAll, 1) decode_step_kernel(const Step
         if (INT4) {
           const __half2 h0a = *reinterpret_cast<const __half2*>(&s0.x), h0b = *reinterpret_cast<const __half2*>(&s0.y);
           const __half2 h1a = *reinterpret_cast<const __half2*>(&s1.x), h1b = *reinterpret_cast<const __half2*>(&s1.y);
-          const float s0a = __low2float(h0a), z0a = __high2float(h0a), s0b = __low2float(h0b), z0b = __high2float(h0b);
-          const float s1a = __low2float(h1a), z1a = __high2float(h1a), s1b = __low2float(h1b), z1b = __high2float(h1b);
+          const float s0a = __low2float(h0a), z0a = __high2float(h0a) + 128.f, s0b = __low2float(h0b), z0b = __high2float(h0b) + 128.f;
+          const float s1a = __low2float(h1a), z1a = __high2float(h1a) + 128.f, s1b = __low2float(h1b), z1b = __high2float(h1b) + 128.f;
 #pragma unroll
           for (int nb = 0; nb < NB; ++nb) {
             const int c0 = 2 * t + 8 * nb;
@@ -708,7 +722,9 @@ static int plan_program(const b200_decode_program* prog, StepPlan* plan, const c
     off += scratch + kDW * 16 * 4 + 16 * 4;
     if (int4) off += ((((size_t)prog->batch * (max_k / 64)) + 3) & ~(size_t)3) * 4;
     off += (((size_t)prog->batch * xstride * 2) + 127) & ~(size_t)127;
-    const size_t lut_at = (off + 0xFFFF) & ~(size_t)0xFFFF, ring_c = lut_at + 0x10000, end = 1024 + (size_t)kDDynSmem;
+    const size_t end = 1024 + (size_t)kDDynSmem;
+    if (int4) return off < end ? (end - off) / stage : 0;   // no table
+    const size_t lut_at = (off + 0xFFFF) & ~(size_t)0xFFFF, ring_c = lut_at + 0x10000;
     if (ring_c > end) return 0;
     return (lut_at - off) / stage + (end - ring_c) / stage;
   };

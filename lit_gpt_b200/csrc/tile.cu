@@ -11,13 +11,31 @@
 //                                            bytes 8..15 = the same bytes of row 16*R + g + 8
 //     [g 0..7][8 B]        float absmax(row 16R+g, kb), float absmax(row 16R+g+8, kb)
 //   INT4 record (1088 B), index R * (nkb/2) + kb/2  (group 128 = two k-blocks share one {scale, zero}):
-//     [2 k-blocks][lane][16 B] as above, then [g][8 B] = half2{scale,zero}(row g), half2{scale,zero}(row g+8)
+//     [2 k-blocks][lane][16 B] as above, then [g][8 B] = half2{scale,zero}(row g), half2{scale,zero}(row g+8);
+//     inside every 32-bit word the 8 codes e0..e7 are re-ordered to e0 e2 e4 e6 | e1 e3 e5 e7 (even elements in the
+//     low half-word, odd ones in the high half-word) so that ((w >> 4p) & 0x000F000F) | 0x43004300 IS the bf16 pair
+//     (128 + e_2p, 128 + e_2p+1): the GEMV dequantises int4 with one shift and one LOP3 per two weights, no table.
 //
 // Rows beyond N (N not a multiple of 16) are zero with scale 0.  The transform is a pure permutation of the
-// reference bytes: b200_untile_4bit reproduces the reference arrays bit for bit (tests/test_gpu_kernels.py).
+// reference bytes (int4: of the reference nibbles): b200_untile_4bit reproduces the reference arrays bit for bit
+// (tests/test_gpu_kernels.py).
 #include "common.cuh"
 
 namespace b200 {
+
+// int4 word: codes e_i at bits 4i  <->  even codes at bits 4p (p = 0..3), odd codes at bits 16 + 4p
+__device__ __forceinline__ uint32_t int4_split_even_odd(uint32_t w) {
+  uint32_t r = 0;
+#pragma unroll
+  for (int p = 0; p < 4; ++p) r |= (((w >> (8 * p)) & 15u) << (4 * p)) | (((w >> (8 * p + 4)) & 15u) << (16 + 4 * p));
+  return r;
+}
+__device__ __forceinline__ uint32_t int4_merge_even_odd(uint32_t w) {
+  uint32_t r = 0;
+#pragma unroll
+  for (int p = 0; p < 4; ++p) r |= (((w >> (4 * p)) & 15u) << (8 * p)) | (((w >> (16 + 4 * p)) & 15u) << (8 * p + 4));
+  return r;
+}
 
 __global__ void __launch_bounds__(256) tile_4bit_kernel(const uint8_t* __restrict__ packed, const uint32_t* __restrict__ scale,
                                                         int64_t N, int64_t K, int int4, uint8_t* __restrict__ out, int64_t nrec_total) {
@@ -40,6 +58,10 @@ __global__ void __launch_bounds__(256) tile_4bit_kernel(const uint8_t* __restric
       uint2 lo = make_uint2(0u, 0u), hi = make_uint2(0u, 0u);
       if (r0 < N) lo = *reinterpret_cast<const uint2*>(packed + r0 * (K >> 1) + kb * 32 + t * 8);
       if (r1 < N) hi = *reinterpret_cast<const uint2*>(packed + r1 * (K >> 1) + kb * 32 + t * 8);
+      if (int4) {
+        lo.x = int4_split_even_odd(lo.x); lo.y = int4_split_even_odd(lo.y);
+        hi.x = int4_split_even_odd(hi.x); hi.y = int4_split_even_odd(hi.y);
+      }
       *reinterpret_cast<uint4*>(dst + b * 512 + lane * 16) = make_uint4(lo.x, lo.y, hi.x, hi.y);
     }
     if (t == 0) {
@@ -68,7 +90,11 @@ __global__ void __launch_bounds__(256) untile_4bit_kernel(const uint8_t* __restr
     const int64_t r0 = R * 16 + g, r1 = r0 + 8;
     for (int b = 0; b < bpr; ++b) {
       const int kb = j * bpr + b;
-      const uint4 v = *reinterpret_cast<const uint4*>(src + b * 512 + lane * 16);
+      uint4 v = *reinterpret_cast<const uint4*>(src + b * 512 + lane * 16);
+      if (int4) {
+        v.x = int4_merge_even_odd(v.x); v.y = int4_merge_even_odd(v.y);
+        v.z = int4_merge_even_odd(v.z); v.w = int4_merge_even_odd(v.w);
+      }
       if (r0 < N) *reinterpret_cast<uint2*>(packed + r0 * (K >> 1) + kb * 32 + t * 8) = make_uint2(v.x, v.y);
       if (r1 < N) *reinterpret_cast<uint2*>(packed + r1 * (K >> 1) + kb * 32 + t * 8) = make_uint2(v.z, v.w);
     }
