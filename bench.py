@@ -314,8 +314,16 @@ def run_ours(args) -> None:
     gemv_ms = time_graph(gg, reps, 1) / reps
     peaks, peak_src = measured_peaks()
     achieved = bytes_step["weights"] / (gemv_ms / 1e3) / 1e9
+    # dram__bytes_read + dram__bytes_write per launch from the committed ncu capture of this workload (ratio to the
+    # algorithmic bytes, measured per layer shape); null for workloads that were not captured
+    traffic = None
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        if tj.get("workload") == args.workload and world == 1:
+            traffic = tj["traffic_over_algorithmic"] * bytes_step["weights"] / max(1, gemv_launches)
     roofline = {"bound": "hbm", "kernel": "qgemv_stream_kernel", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
                 "launches_per_step": gemv_launches, "avg_launch_us": gemv_ms * 1e3 / max(1, gemv_launches),
                 "algorithmic_bytes_per_launch": bytes_step["weights"] / max(1, gemv_launches),
                 "whole_step_frac": bytes_step["total"] / (ms / K_steps / 1e3) / 1e9 / peaks["hbm_gbs"],
