@@ -52,6 +52,14 @@ int b200_quantize_4bit(const void* w, int w_dtype, int64_t numel, int blocksize,
                        float* absmax, b200_stream_t stream);
 int b200_dequantize_4bit(const uint8_t* packed, const float* absmax, int64_t numel, int blocksize, int qtype,
                          void* out, int out_dtype, b200_stream_t stream);
+/* Double quantisation of an absmax vector (--quantize bnb.nf4-dq / bnb.fp4-dq; bitsandbytes quantize_4bit with
+ * compress_statistics=True, reference call sites generate/base.py:105,129-134): blocks of 256, `offset` (the mean,
+ * computed by the caller) is subtracted, block absmax -> absmax2, 8-bit index into the 256-entry dynamic code
+ * (code256, sorted ascending) -> q_out, and absmax_deq_out = code[q] * absmax2 + offset, the value every later
+ * dequantise / GEMV of the layer uses.  n values in, ceil(n / 256) absmax2 out. */
+int b200_double_quant_absmax(const float* absmax, int64_t n, const float* code256, float offset, uint8_t* q_out, float* absmax2_out,
+                             float* absmax_deq_out, b200_stream_t stream);
+
 /* int4 group-128 (asymmetric RTN, GPTQ storage order): qweight uint32 (N, ceil(K/8)), scales fp16 (N, G),
  * qzeros uint32 (N, ceil(G/8)), G = ceil(K/group).  `sz` (optional, may be NULL) receives the kernel-side
  * interleaved half2 {scale, zero} per (row, group) that b200_qgemv consumes. */

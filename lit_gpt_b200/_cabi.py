@@ -87,6 +87,7 @@ _SIGNATURES = {
     "b200_qgemv_tune": (c_int, [c_int, c_int, c_int]),
     "b200_quantize_4bit": (c_int, [c_void_p, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "b200_dequantize_4bit": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int, c_void_p]),
+    "b200_double_quant_absmax": (c_int, [c_void_p, c_int64, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200_quantize_int4": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200_dequantize_int4": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_int, c_void_p]),
     "b200_qgemv_workspace_bytes": (c_size_t, []),

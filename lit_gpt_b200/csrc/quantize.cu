@@ -167,6 +167,46 @@ __global__ void __launch_bounds__(256) dequantize_int4_kernel(const uint32_t* __
   }
 }
 
+
+// ---- double quantisation of the absmax vector (bnb.nf4-dq / fp4-dq): per 256 values, subtract the
+// caller-given offset (mean), take the block absmax, map x / absmax2 to the nearest entry of the 256-entry
+// "dynamic" code with bitsandbytes' pivot search (kernels.cu dQuantize<0>), and write back the DEQUANTISED value
+// code[q] * absmax2 + offset, which is what every later dequantise / GEMV of a -dq layer uses.
+__global__ void __launch_bounds__(256) double_quant_absmax_kernel(const float* __restrict__ absmax, int64_t n, const float* __restrict__ code,
+                                                                  float offset, uint8_t* __restrict__ q_out, float* __restrict__ absmax2_out,
+                                                                  float* __restrict__ deq_out) {
+  __shared__ float s_code[256];
+  __shared__ float s_max[8];
+  griddep_wait();
+  const int tid = threadIdx.x;
+  s_code[tid] = code[tid];
+  const int64_t i = (int64_t)blockIdx.x * 256 + tid;
+  const float v = i < n ? __fsub_rn(absmax[i], offset) : 0.f;
+  float m = warp_max(fabsf(v));
+  if ((tid & 31) == 0) s_max[tid >> 5] = m;
+  __syncthreads();
+  m = s_max[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) m = fmaxf(m, s_max[w]);
+  if (tid == 0) absmax2_out[blockIdx.x] = m;
+  if (i >= n) return;
+  const float x = __fmul_rn(v, __fdiv_rn(1.0f, m));
+  int pivot = 127, upper_pivot = 255, lower_pivot = 0;
+  float lower = -1.0f, upper = 1.0f, val = s_code[pivot];
+  for (int st = 64; st > 0; st >>= 1) {
+    if (x > val) { lower_pivot = pivot; lower = val; pivot += st; }
+    else { upper_pivot = pivot; upper = val; pivot -= st; }
+    val = s_code[pivot];
+  }
+  if (upper_pivot == 255) upper = s_code[upper_pivot];
+  if (lower_pivot == 0) lower = s_code[lower_pivot];
+  int q;
+  if (x > val) q = x > __fmul_rn(__fadd_rn(upper, val), 0.5f) ? upper_pivot : pivot;
+  else q = x < __fmul_rn(__fadd_rn(lower, val), 0.5f) ? lower_pivot : pivot;
+  q_out[i] = (uint8_t)q;
+  deq_out[i] = __fadd_rn(__fmul_rn(s_code[q], m), offset);
+}
+
 static int grid_for(int64_t work_items, int per_block) {
   int64_t blocks = (work_items + per_block - 1) / per_block;
   int64_t cap = (int64_t)sm_count() * 16;
@@ -245,6 +285,15 @@ int b200_dequantize_int4(const uint32_t* qweight, const uint16_t* scales, const 
     case B200_F32: B200_CUDA(launch(dequantize_int4_kernel<float>, dim3(grid), dim3(256), 0, st, qweight, scales, qzeros, N, K, group, (float*)out)); break;
     default: B200_CHECK_ARG(false, "b200_dequantize_int4: unsupported dtype %d", out_dtype);
   }
+  return B200_OK;
+}
+
+int b200_double_quant_absmax(const float* absmax, int64_t n, const float* code256, float offset, uint8_t* q_out, float* absmax2_out,
+                             float* absmax_deq_out, b200_stream_t stream) {
+  B200_CHECK_ARG(absmax && code256 && q_out && absmax2_out && absmax_deq_out, "b200_double_quant_absmax: null pointer");
+  B200_CHECK_ARG(n > 0 && (n + 255) / 256 <= 0x7fffffff, "b200_double_quant_absmax: bad length %lld", (long long)n);
+  B200_CUDA(launch(double_quant_absmax_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, (cudaStream_t)stream, absmax, n, code256, offset,
+                   q_out, absmax2_out, absmax_deq_out));
   return B200_OK;
 }
 

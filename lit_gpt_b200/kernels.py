@@ -62,6 +62,46 @@ def dequantize_4bit(packed: torch.Tensor, absmax: torch.Tensor, shape, dtype: to
     return out
 
 
+_dynamic_map_cache: Dict[int, torch.Tensor] = {}
+
+
+def dynamic_map(device: torch.device) -> torch.Tensor:
+    """bitsandbytes' 256-entry signed 8-bit "dynamic" code (functional.create_dynamic_map(signed=True, 7, 8)), sorted."""
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    if key not in _dynamic_map_cache:
+        import numpy as np
+
+        f32 = np.float32
+        data = []
+        for i in range(7):
+            items = int(2 ** i + 1)
+            b = np.linspace(0.1, 1, items, dtype=f32)
+            means = ((b[:-1] + b[1:]) / f32(2.0)).astype(f32)
+            scale = 10 ** (-6 + i)
+            data += (scale * means.astype(np.float64)).tolist() + (-scale * means.astype(np.float64)).tolist()
+        data += [0, 1.0]
+        data += [0] * (256 - len(data))
+        data.sort()
+        _dynamic_map_cache[key] = torch.tensor(np.array(data, dtype=f32), device=device)
+    return _dynamic_map_cache[key]
+
+
+def double_quant_absmax(absmax: torch.Tensor, offset: Optional[float] = None):
+    """-> (q uint8 [n], absmax2 fp32 [ceil(n/256)], offset float, absmax_dequantised fp32 [n])  (SURVEY Q2)."""
+    C.require_cuda(absmax)
+    absmax = absmax.contiguous().float()
+    n = absmax.numel()
+    if offset is None:
+        offset = float(absmax.mean())
+    q = torch.empty(n, dtype=torch.uint8, device=absmax.device)
+    a2 = torch.empty((n + 255) // 256, dtype=torch.float32, device=absmax.device)
+    deq = torch.empty_like(absmax)
+    code = dynamic_map(absmax.device)
+    C.check(C.load().b200_double_quant_absmax(absmax.data_ptr(), n, code.data_ptr(), offset, q.data_ptr(), a2.data_ptr(), deq.data_ptr(),
+                                              C.stream_ptr(absmax.device)), "double_quant_absmax")
+    return q, a2, offset, deq
+
+
 def quantize_int4(w: torch.Tensor, group: int = 128):
     """-> (qweight uint32-as-int32 (N, ceil(K/8)), scales fp16 (N, G), qzeros int32 (N, ceil(G/8)), sz int32 (N, G))."""
     C.require_cuda(w)

@@ -40,12 +40,11 @@ class QLinear(nn.Module):
             raise ValueError(f"unknown quantization mode {mode!r}; expected one of {MODES}")
         if mode == "int8":
             raise NotImplementedError("bnb.int8 (LLM.int8()) is specified in oracle/quant_ref.py but has no CUDA kernel yet")
-        if mode.endswith("-dq"):
-            raise NotImplementedError(f"{mode}: double quantisation of absmax is specified in oracle/quant_ref.py but "
-                                      "has no CUDA kernel yet; use the non-dq mode")
         self.in_features, self.out_features = in_features, out_features
         self.mode, self.compute_dtype = mode, compute_dtype
         self.quant_type = mode.split("-")[0]  # nf4 | fp4 | int4
+        self.double_quant = mode.endswith("-dq")  # compress_statistics=True: absmax itself 8-bit quantised
+        self.absmax: Optional[torch.Tensor] = None  # fp32 absmax the kernels read (for -dq: the dequantised statistics)
         self.blocksize = 128 if self.quant_type == "int4" else 64
         kw = dict(device=device, dtype=dtype)
         self.weight = nn.Parameter(torch.empty((out_features, in_features), **kw), requires_grad=False)
@@ -77,7 +76,7 @@ class QLinear(nn.Module):
     @property
     def scale(self) -> torch.Tensor:
         """The per-block scale tensor the kernels consume (fp32 absmax, or packed half2 {scale, zero} for int4)."""
-        return self.sz if self.quant_type == "int4" else self.quant_state[0]
+        return self.sz if self.quant_type == "int4" else self.absmax
 
     @torch.no_grad()
     def quantize_(self) -> None:
@@ -101,7 +100,15 @@ class QLinear(nn.Module):
         else:
             packed, absmax = K.quantize_4bit(w, self.quant_type, self.blocksize)
             self.weight = nn.Parameter(packed, requires_grad=False)
-            self.quant_state = [absmax, torch.Size(shape), w.dtype, self.blocksize, None, self.quant_type, None]
+            if self.double_quant:
+                # bitsandbytes 0.41 nested form: quant_state[0] = 8-bit absmax, [4] = [offset, [absmax2, code, 256]];
+                # the kernels stream the fp32 statistics expanded once here (0.5625 B/param in HBM, 0.5159 on disk)
+                qabs, absmax2, offset, absmax = K.double_quant_absmax(absmax)
+                self.quant_state = [qabs, torch.Size(shape), w.dtype, self.blocksize, [offset, [absmax2, K.dynamic_map(w.device), 256]],
+                                    self.quant_type, None]
+            else:
+                self.quant_state = [absmax, torch.Size(shape), w.dtype, self.blocksize, None, self.quant_type, None]
+            self.absmax = absmax
         if self.bias is not None and self.bias.dtype != self.compute_dtype:
             self.bias = nn.Parameter(self.bias.data.to(self.compute_dtype), requires_grad=False)
         self.tiled = None
@@ -116,7 +123,7 @@ class QLinear(nn.Module):
         shape = self.quant_state[1]
         if self.quant_type == "int4":
             return K.dequantize_int4(self.weight.data, self.scales, self.qzeros, shape[1], self.blocksize, dtype)
-        return K.dequantize_4bit(self.weight.data, self.quant_state[0], shape, dtype, self.quant_type, self.blocksize)
+        return K.dequantize_4bit(self.weight.data, self.absmax, shape, dtype, self.quant_type, self.blocksize)
 
     # -- device moves trigger quantization (bitsandbytes: Params4bit.cuda()) --------------------------------
     def _apply(self, fn, recurse: bool = True):
@@ -129,7 +136,10 @@ class QLinear(nn.Module):
                     raise B200Error("a quantized QLinear cannot leave CUDA (no CPU path)")
                 self.weight = nn.Parameter(self.weight.data.to(dev), requires_grad=False)
                 self.quant_state[0] = self.quant_state[0].to(dev)
-                for name in ("scales", "qzeros", "sz", "tiled"):
+                if self.double_quant:
+                    self.quant_state[4][1][0] = self.quant_state[4][1][0].to(dev)
+                    self.quant_state[4][1][1] = self.quant_state[4][1][1].to(dev)
+                for name in ("scales", "qzeros", "sz", "tiled", "absmax"):
                     t = getattr(self, name)
                     if t is not None:
                         setattr(self, name, t.to(dev))
@@ -151,7 +161,7 @@ class QLinear(nn.Module):
                                   f"({self.out_features}, {self.in_features})")
                 return
             target = self.weight.device
-            self.quant_state, self.scales, self.qzeros, self.sz, self.tiled = None, None, None, None, None
+            self.quant_state, self.scales, self.qzeros, self.sz, self.tiled, self.absmax = None, None, None, None, None, None
             if target.type == "cuda":
                 self.weight = nn.Parameter(w.detach().to(target), requires_grad=False)
                 self.quantize_()

@@ -230,10 +230,11 @@ def dequantize_blockwise8(q, absmax2, blocksize: int = 256, code: np.ndarray = D
     return (code[q] * scale).astype(F32)
 
 
-def double_quantize_absmax(absmax: np.ndarray):
-    """quantize_4bit(compress_statistics=True): offset = mean; absmax -= offset; 8-bit blockwise (256)."""
+def double_quantize_absmax(absmax: np.ndarray, offset=None):
+    """quantize_4bit(compress_statistics=True): offset = mean; absmax -= offset; 8-bit blockwise (256).
+    `offset` may be given (a GPU mean reduces in a different order than numpy's; the rest is order-independent)."""
     absmax = np.asarray(absmax, F32)
-    offset = F32(absmax.mean(dtype=F32))
+    offset = F32(absmax.mean(dtype=F32)) if offset is None else F32(offset)
     q, absmax2 = quantize_blockwise8((absmax - offset).astype(F32), 256)
     return q, absmax2, offset
 

@@ -454,3 +454,40 @@ def test_qgemm_unsupported_shapes(K):
     w, _, packed, scale, bs, _ = _gemv_case(K, 20, 96, 1, "nf4")
     with pytest.raises(NotImplementedError):
         K.qgemm(torch.zeros(32, 96, dtype=torch.bfloat16, device="cuda"), packed, scale, 20, 96, "nf4", 64)
+
+
+# ---- double quantisation of absmax (bnb.nf4-dq / fp4-dq) ---------------------------------------------------------
+def test_double_quant_absmax_bit_exact(K):
+    g = torch.Generator().manual_seed(11)
+    for n in (256, 1000, 4096 * 64, 5):
+        a = (torch.rand(n, generator=g) * 0.08 + 0.01).float()
+        if n == 1000:
+            a[300:556] = 0.05  # a block whose centred values are all equal
+        q, a2, off, deq = K.double_quant_absmax(a.cuda())
+        q_ref, a2_ref, off_ref = Q.double_quantize_absmax(a.numpy(), offset=off)
+        assert np.array_equal(q.cpu().numpy(), q_ref) and np.array_equal(a2.cpu().numpy(), a2_ref)
+        assert np.array_equal(deq.cpu().numpy(), Q.dequantize_absmax(q_ref, a2_ref, off_ref))
+        assert abs(off - float(a.mean())) <= 1e-6
+    assert np.array_equal(K.dynamic_map(torch.device("cuda")).cpu().numpy(), Q.DYNAMIC_MAP)
+
+
+@pytest.mark.parametrize("mode", ["nf4-dq", "fp4-dq"])
+def test_qlinear_double_quant_modes(K, mode):
+    """--quantize bnb.nf4-dq: weights dequantise to code * dequant8(absmax) exactly as the oracle says, and the GEMV /
+    prefill GEMM of such a layer agree with the dequantised matrix."""
+    from lit_gpt_b200.quant import QLinear
+
+    qt = mode.split("-")[0]
+    w = _randw((512, 1024), 21)
+    lin = QLinear(1024, 512, bias=False, mode=mode)
+    lin.weight.data = w.clone()
+    lin = lin.cuda()
+    assert lin.is_quantized and lin.quant_state[0].dtype == torch.uint8 and lin.quant_state[4] is not None
+    packed, absmax = QC.quantize_4bit(w.float().numpy(), qt)
+    qa, a2, off = Q.double_quantize_absmax(absmax, offset=lin.quant_state[4][0])
+    deq = QC.dequantize_4bit(packed, Q.dequantize_absmax(qa, a2, off), (512, 1024), qt)
+    assert torch.equal(lin.dequantize(torch.float32).cpu(), torch.from_numpy(deq))
+    x = _randw((1, 1024), 22, std=1.0)
+    _check_gemv(lin(x.cuda()).cpu(), x, torch.from_numpy(deq))
+    xm = _randw((64, 1024), 23, std=1.0)
+    _check_gemv(lin(xm.cuda()).cpu(), xm, torch.from_numpy(deq))
