@@ -3,6 +3,8 @@
 // Replaces, for T > 16 rows, bnb.nn.Linear4bit.forward's "dequantize_4bit of the WHOLE weight to bf16, then F.linear"
 // (call sites lit_gpt/model.py:519,619,656,713,714,716): the bf16 weight is never materialised in HBM.
 // Each CTA owns a (128 * MT tokens) x (128 output features) tile and walks K in blocks of 64:
+//   * the ACTIVATION tiles (128 tokens x 64 k, bf16) are fetched by TMA (cp.async.bulk.tensor.2d over a tensor map of x,
+//     SWIZZLE_128B, rows past M zero-filled by the hardware) straight into the tensor core's K-major layout;
 //   * 16 PRODUCER warps read the packed 4-bit weights (8 B = 16 codes per thread per k-block) and their absmax /
 //     {scale, zero}, rebuild the bf16 values with exactly the dequantise kernel's arithmetic
 //     (bf16_rn(code_fp32 * absmax_fp32), resp. bf16_rn(scale * (q - zero))) and write them, together with the
@@ -14,6 +16,8 @@
 //     (32 lanes x 32 columns per warp and instruction), add the bias, round to bf16 and store rows of y.
 // With MT = 2 one dequantised weight tile feeds 256 tokens, so the CUDA-core dequant (~500 clk per k-block) is
 // hidden under the tensor-core time (2 x 256 clk).
+#include <cuda.h>  // CUtensorMap (type only; the encoder is resolved at run time through the runtime, no -lcuda)
+
 #include "common.cuh"
 
 namespace b200 {
@@ -72,7 +76,7 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {  // arrives on `bar`
 __device__ __forceinline__ uint32_t sw128(int r, int c) { return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4)); }
 
 template <int MT>
-__global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmParams p) {
+__global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x) {
   extern __shared__ __align__(1024) uint8_t g_smem[];
   constexpr int STAGE = (MT + 1) * kTileBytes;      // MT activation tiles + 1 weight tile
   constexpr int TMEM_COLS = 128 * MT;
@@ -89,7 +93,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
   const bool int4 = p.qtype == B200_Q_INT4;
 
   if (tid == 0) {
-    for (int s = 0; s < kGStages; ++s) { g_mbar_init(full0 + s * 8, 2 * (kGProducers / 32)); g_mbar_init(empty0 + s * 8, 1); }
+    for (int s = 0; s < kGStages; ++s) { g_mbar_init(full0 + s * 8, kGProducers / 32 + 1); g_mbar_init(empty0 + s * 8, 1); }
     g_mbar_init(done_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -109,11 +113,10 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
 
   if (warp < kGProducers / 32) {
     // =========================================== PRODUCERS ======================================================
-    // Software pipeline per thread: the activation tile of k-block kb is fetched with cp.async (16 B, zero-filled past
-    // M) straight into its swizzled slot and only waited for kALag iterations later; the packed weights and scales are
-    // prefetched into registers kWLag k-blocks ahead.  full[s] therefore collects TWO arrivals per warp and phase: one
-    // for the dequantised weight tile (iteration kb), one for the activation tile (iteration kb + kALag).
-    constexpr int kALag = 2, kWLag = 2;
+    // The activation tiles of k-block kb are requested by ONE thread with TMA (no LSU work, no registers); the packed
+    // weights and scales are prefetched into registers kWLag k-blocks ahead.  full[s] collects one arrival per warp
+    // (dequantised weight tile written) plus the TMA thread's expect_tx arrival; the TMA bytes complete the phase.
+    constexpr int kWLag = 2;
     // weight tile: thread -> (row r = tid / 4, quarter h = tid % 4): 8 packed bytes = k [16h, 16h + 16) of the k-block
     const int wr = tid >> 2, wh = tid & 3;
     const int64_t wn = n0 + wr;
@@ -128,30 +131,21 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
       scn[i] = 0u;
       if (wvalid && i < nkb) { qn[i] = ldg_stream_v2(wsrc + (int64_t)i * 32); scn[i] = ssrc[int4 ? (i >> 1) : i]; }
     }
-    // activation chunks of this thread: rows r_i = (i * 512 + tid) / 8, chunk c = tid % 8 (fixed); source pointers and
-    // swizzled destinations are loop-invariant up to the k-block / stage offset
-    constexpr int ACH = (128 * MT * 8) / kGProducers;
-    const int ac = tid & 7;
-    const __nv_bfloat16* asrc[ACH];
-    uint32_t adst[ACH], asz[ACH];
-#pragma unroll
-    for (int i = 0; i < ACH; ++i) {
-      const int r = (i * kGProducers + tid) >> 3;
-      const int64_t m = m0 + r;
-      asz[i] = m < p.M ? 16u : 0u;
-      asrc[i] = p.x + (m < p.M ? m : 0) * p.K + ac * 8;
-      adst[i] = tiles_a + (uint32_t)((r >> 7) * kTileBytes) + sw128(r & 127, ac);
-    }
     const uint32_t wdst0 = (uint32_t)(MT * kTileBytes) + sw128(wr, wh * 2), wdst1 = (uint32_t)(MT * kTileBytes) + sw128(wr, wh * 2 + 1);
     for (int kb = 0; kb < nkb; ++kb) {
       const int s = kb % kGStages;
       if (kb >= kGStages) g_mbar_wait(empty0 + s * 8, ((kb / kGStages) - 1) & 1);
       uint8_t* st = tiles + (size_t)s * STAGE;
-      // ---- activation tiles: 128 * MT rows x 8 chunks of 16 B, coalesced along K, asynchronous ----------------------
+      // ---- activation tiles: MT boxes of 128 rows x 64 k by TMA, issued by one thread ------------------------------
+      if (tid == 0) {
+        const uint32_t bar = full0 + s * 8;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(MT * kTileBytes) : "memory");
 #pragma unroll
-      for (int i = 0; i < ACH; ++i)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(adst[i] + (uint32_t)(s * STAGE)), "l"(asrc[i] + (int64_t)kb * kBK), "r"(asz[i]) : "memory");
-      asm volatile("cp.async.commit_group;" ::: "memory");
+        for (int mt = 0; mt < MT; ++mt)
+          asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                       ::"r"(tiles_a + (uint32_t)(s * STAGE + mt * kTileBytes)), "l"(&tmap_x), "r"(kb * kBK), "r"((int)(m0 + mt * 128)), "r"(bar)
+                       : "memory");
+      }
       // ---- weight tile: dequantise 16 codes -> 2 chunks of 8 bf16 ----------------------------------------------------
       const uint2 q = qn[0];
       const uint32_t sc = scn[0];
@@ -192,19 +186,9 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
           *reinterpret_cast<uint4*>(st + (j ? wdst1 : wdst0)) = make_uint4(o[0], o[1], o[2], o[3]);
         }
       }
-      asm volatile("cp.async.wait_group %0;" ::"n"(kALag) : "memory");   // this thread's activation chunks of kb - kALag landed
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // generic-proxy writes -> visible to the tensor core
       __syncwarp();
-      if (lane == 0) {
-        g_mbar_arrive(full0 + s * 8);                                                    // weight tile of kb
-        if (kb >= kALag) g_mbar_arrive(full0 + ((kb - kALag) % kGStages) * 8);           // activation tiles of kb - kALag
-      }
-    }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncwarp();
-    if (lane == 0) {
-      for (int kb = nkb > kALag ? nkb - kALag : 0; kb < nkb; ++kb) g_mbar_arrive(full0 + (kb % kGStages) * 8);
+      if (lane == 0) g_mbar_arrive(full0 + s * 8);                       // weight tile of kb
     }
   } else if (lane == 0) {
     // =========================================== MMA ISSUER =====================================================
@@ -272,6 +256,19 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
   }
 }
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
 template <int MT>
 static cudaError_t launch_gemm(const GemmParams& p, cudaStream_t st) {
   constexpr int smem = kGStages * (MT + 1) * kTileBytes + 1024;
@@ -281,8 +278,19 @@ static cudaError_t launch_gemm(const GemmParams& p, cudaStream_t st) {
     if (e != cudaSuccess) return e;
     configured = true;
   }
+  // tensor map of x (M, K) bf16 row-major: dim0 = K (contiguous), dim1 = M; box 64 x 128, 128-byte swizzle, zero fill
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) return cudaErrorNotSupported;
+  alignas(64) CUtensorMap tmap;
+  const cuuint64_t gdim[2] = {(cuuint64_t)p.K, (cuuint64_t)p.M};
+  const cuuint64_t gstride[1] = {(cuuint64_t)p.K * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)kBK, 128u};
+  const cuuint32_t estr[2] = {1u, 1u};
+  if (enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(p.x), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return cudaErrorInvalidValue;
   dim3 grid((unsigned)((p.N + kBN - 1) / kBN), (unsigned)((p.M + 128 * MT - 1) / (128 * MT)));
-  return launch(qgemm_tcgen05_kernel<MT>, grid, dim3(kGThreads), (size_t)smem, st, p);
+  return launch(qgemm_tcgen05_kernel<MT>, grid, dim3(kGThreads), (size_t)smem, st, p, tmap);
 }
 
 }  // namespace b200
