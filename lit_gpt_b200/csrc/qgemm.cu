@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
     for (int kb = 0; kb < nkb; ++kb) {
       const int s = kb % kGStages;
       if (kb >= kGStages) g_mbar_wait(empty0 + s * 8, ((kb / kGStages) - 1) & 1);
-      uint8_t* st = tiles + (size_t)s * STAGE;
+      const uint32_t st_a = tiles_a + (uint32_t)(s * STAGE);   // shared-window address: explicit st.shared, not generic stores
       // ---- activation tiles: MT boxes of 128 rows x 64 k by TMA, issued by one thread ------------------------------
       if (tid == 0) {
         const uint32_t bar = full0 + s * 8;
@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
             const float b = scale * ((float)((qw[j] >> (8 * e + 4)) & 15u) - zero);
             o[e] = pack_bf16(a, b);
           }
-          *reinterpret_cast<uint4*>(st + (j ? wdst1 : wdst0)) = make_uint4(o[0], o[1], o[2], o[3]);
+          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(st_a + (j ? wdst1 : wdst0)), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
         }
       } else {
         const float am = __uint_as_float(sc);
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
             const uint32_t byte = (qw[j] >> (8 * e)) & 255u;
             o[e] = pack_bf16(code[(byte >> 4) * 32] * am, code[(byte & 15u) * 32] * am);
           }
-          *reinterpret_cast<uint4*>(st + (j ? wdst1 : wdst0)) = make_uint4(o[0], o[1], o[2], o[3]);
+          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(st_a + (j ? wdst1 : wdst0)), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
         }
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // generic-proxy writes -> visible to the tensor core
