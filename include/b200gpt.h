@@ -273,6 +273,29 @@ typedef struct b200_qgemm_args {
 size_t b200_qgemm_workspace_bytes(int64_t M, int64_t N, int64_t K);
 int b200_qgemm(const b200_qgemm_args* args, b200_stream_t stream);
 
+/* ---- bnb.int8: LLM.int8() inference Linear (replaces bitsandbytes.nn.Linear8bitLt(has_fp16_weights=False,
+ *      threshold=6.0) installed by BitsandbytesPrecision("int8") at generate/base.py:129-134; arithmetic restated in
+ *      oracle/quant_ref.py:310-345).  Implemented in csrc/int8.cu.
+ *      b200_quantize_int8: CB = rint(W * 127 / absmax_row) int8 (N, K), SCB = absmax_row fp32 (N).
+ *      b200_linear_int8:   y (M, N) fp16 = LLM.int8()(x (M, K) fp16): outlier columns (any |x| >= threshold) through an
+ *      fp16 side product, the rest int8 x int8 -> int32 on the tensor cores.  K must be a multiple of 64
+ *      (else B200_ERR_UNSUPPORTED).  The workspace holds the quantised activations; nothing is allocated inside. */
+int b200_quantize_int8(const void* w, int w_dtype, int64_t N, int64_t K, int8_t* cb, float* scb, b200_stream_t stream);
+int b200_dequantize_int8(const int8_t* cb, const float* scb, int64_t N, int64_t K, void* out, int out_dtype, b200_stream_t stream);
+typedef struct b200_linear_int8_args {
+  const void* x;      /* (M, K) fp16 */
+  const void* cb;     /* (N, K) int8 */
+  const void* scb;    /* (N) fp32 */
+  const void* bias;   /* (N) fp16 or NULL */
+  void* y;            /* (M, N) fp16 */
+  int64_t M, N, K;
+  float threshold;    /* 6.0 in the reference; <= 0 disables the outlier path */
+  void* workspace;
+  size_t workspace_bytes;
+} b200_linear_int8_args;
+size_t b200_linear_int8_workspace_bytes(int64_t M, int64_t K);
+int b200_linear_int8(const b200_linear_int8_args* args, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

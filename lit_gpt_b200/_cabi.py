@@ -19,6 +19,12 @@ EPI_STORE, EPI_RESIDUAL, EPI_SWIGLU = 0, 1, 2
 DTYPE_CODE = {torch.bfloat16: BF16, torch.float16: F16, torch.float32: F32}
 
 
+class LinearInt8Args(ctypes.Structure):  # mirrors b200_linear_int8_args
+    _fields_ = [("x", c_void_p), ("cb", c_void_p), ("scb", c_void_p), ("bias", c_void_p), ("y", c_void_p),
+                ("M", c_int64), ("N", c_int64), ("K", c_int64), ("threshold", c_float), ("workspace", c_void_p),
+                ("workspace_bytes", c_size_t)]
+
+
 class QGemvArgs(ctypes.Structure):
     _fields_ = [
         ("packed", c_void_p), ("scale", c_void_p), ("packed2", c_void_p), ("scale2", c_void_p),
@@ -88,6 +94,10 @@ _SIGNATURES = {
     "b200_quantize_4bit": (c_int, [c_void_p, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "b200_dequantize_4bit": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int, c_void_p]),
     "b200_double_quant_absmax": (c_int, [c_void_p, c_int64, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "b200_quantize_int8": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "b200_dequantize_int8": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int, c_void_p]),
+    "b200_linear_int8_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "b200_linear_int8": (c_int, [ctypes.POINTER(LinearInt8Args), c_void_p]),
     "b200_quantize_int4": (c_int, [c_void_p, c_int, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200_dequantize_int4": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_int, c_void_p]),
     "b200_qgemv_workspace_bytes": (c_size_t, []),

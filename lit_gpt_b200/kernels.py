@@ -102,6 +102,58 @@ def double_quant_absmax(absmax: torch.Tensor, offset: Optional[float] = None):
     return q, a2, offset, deq
 
 
+# ---------------------------------------------------------------------------------------------------------
+# bnb.int8 (LLM.int8())
+# ---------------------------------------------------------------------------------------------------------
+def quantize_int8(w: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """-> (CB int8 (N, K), SCB fp32 (N)) — Linear8bitLt's row-wise weight quantisation (oracle/quant_ref.py:312-320)."""
+    C.require_cuda(w)
+    if w.dim() != 2 or w.dtype not in C.DTYPE_CODE:
+        raise C.B200Error(f"quantize_int8 expects a 2-D floating-point weight (got {tuple(w.shape)}, {w.dtype})")
+    w = w.contiguous()
+    N, K = w.shape
+    cb = torch.empty((N, K), dtype=torch.int8, device=w.device)
+    scb = torch.empty((N,), dtype=torch.float32, device=w.device)
+    C.check(C.load().b200_quantize_int8(w.data_ptr(), C.DTYPE_CODE[w.dtype], N, K, cb.data_ptr(), scb.data_ptr(),
+                                        C.stream_ptr(w.device)), "quantize_int8")
+    return cb, scb
+
+
+def dequantize_int8(cb: torch.Tensor, scb: torch.Tensor, dtype: torch.dtype = torch.float16) -> torch.Tensor:
+    C.require_cuda(cb, scb)
+    N, K = cb.shape
+    out = torch.empty((N, K), dtype=dtype, device=cb.device)
+    C.check(C.load().b200_dequantize_int8(cb.data_ptr(), scb.data_ptr(), N, K, out.data_ptr(), C.DTYPE_CODE[dtype],
+                                          C.stream_ptr(cb.device)), "dequantize_int8")
+    return out
+
+
+def linear_int8(x: torch.Tensor, cb: torch.Tensor, scb: torch.Tensor, bias: Optional[torch.Tensor] = None,
+                threshold: float = 6.0) -> torch.Tensor:
+    """LLM.int8() forward: x (..., K) fp16 -> (..., N) fp16 (MatMul8bitLt inference path, oracle/quant_ref.py:326-345)."""
+    C.require_cuda(x, cb, scb, bias)
+    if x.dtype != torch.float16:
+        raise C.B200Error(f"linear_int8 computes in fp16 like bitsandbytes (got {x.dtype}); cast the activation first")
+    N, K = cb.shape
+    if x.shape[-1] != K:
+        raise C.B200Error(f"linear_int8: activation has {x.shape[-1]} features, weight expects {K}")
+    x2 = x.reshape(-1, K)
+    x2 = x2 if x2.is_contiguous() else x2.contiguous()
+    M = x2.shape[0]
+    y = torch.empty((M, N), dtype=torch.float16, device=x.device)
+    if M == 0:
+        return y.reshape(*x.shape[:-1], N)
+    if bias is not None and bias.dtype != torch.float16:
+        bias = bias.to(torch.float16)
+    lib = C.load()
+    ws = _ws("int8", x.device, int(lib.b200_linear_int8_workspace_bytes(M, K)))
+    a = C.LinearInt8Args(x=x2.data_ptr(), cb=cb.data_ptr(), scb=scb.data_ptr(), bias=None if bias is None else bias.data_ptr(),
+                         y=y.data_ptr(), M=M, N=N, K=K, threshold=float(threshold), workspace=ws.data_ptr(),
+                         workspace_bytes=ws.numel())
+    C.check(lib.b200_linear_int8(ctypes.byref(a), C.stream_ptr(x.device)), "linear_int8")
+    return y.reshape(*x.shape[:-1], N)
+
+
 def quantize_int4(w: torch.Tensor, group: int = 128):
     """-> (qweight uint32-as-int32 (N, ceil(K/8)), scales fp16 (N, G), qzeros int32 (N, ceil(G/8)), sz int32 (N, G))."""
     C.require_cuda(w)

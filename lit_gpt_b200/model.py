@@ -162,7 +162,8 @@ class GPT(nn.Module):
             return False
 
         def ok(lin: nn.Module) -> bool:
-            return isinstance(lin, QLinear) and lin.is_quantized and lin.weight.is_cuda and lin.bias is None
+            return (isinstance(lin, QLinear) and lin.is_quantized and lin.weight.is_cuda and lin.bias is None
+                    and lin.quant_type != "int8")
 
         for block in self.transformer.h:
             a, m = block.attn, block.mlp
@@ -427,7 +428,7 @@ class LLaMAMLP(nn.Module):
         rows = x.numel() // x.size(-1)
         if (isinstance(f1, QLinear) and isinstance(f2, QLinear) and f1.is_quantized and f2.is_quantized and x.is_cuda
                 and x.dtype == torch.bfloat16 and rows <= 16 and f1.bias is None and f2.bias is None
-                and f1.quant_type == f2.quant_type):
+                and f1.quant_type == f2.quant_type and f1.quant_type != "int8"):
             # gate and up projections + SwiGLU in one pass over both weight matrices
             return self.proj(f1.gemv(x, other=f2))
         x_fc_1 = self.fc_1(x)

@@ -38,11 +38,11 @@ class QLinear(nn.Module):
         super().__init__()
         if mode not in MODES:
             raise ValueError(f"unknown quantization mode {mode!r}; expected one of {MODES}")
-        if mode == "int8":
-            raise NotImplementedError("bnb.int8 (LLM.int8()) is specified in oracle/quant_ref.py but has no CUDA kernel yet")
         self.in_features, self.out_features = in_features, out_features
         self.mode, self.compute_dtype = mode, compute_dtype
-        self.quant_type = mode.split("-")[0]  # nf4 | fp4 | int4
+        self.quant_type = mode.split("-")[0]  # nf4 | fp4 | int4 | int8
+        self.threshold = 6.0  # int8 only: LLM.int8() outlier threshold (Linear8bitLt(threshold=6.0))
+        self.SCB: Optional[torch.Tensor] = None  # int8 only: per-row absmax (bitsandbytes Int8Params.SCB); weight holds CB
         self.double_quant = mode.endswith("-dq")  # compress_statistics=True: absmax itself 8-bit quantised
         self.absmax: Optional[torch.Tensor] = None  # fp32 absmax the kernels read (for -dq: the dequantised statistics)
         self.blocksize = 128 if self.quant_type == "int4" else 64
@@ -92,6 +92,15 @@ class QLinear(nn.Module):
         shape = tuple(w.shape)
         if shape != (self.out_features, self.in_features):
             raise B200Error(f"weight shape {shape} does not match ({self.out_features}, {self.in_features})")
+        if self.quant_type == "int8":
+            cb, scb = K.quantize_int8(w)
+            self.weight = nn.Parameter(cb, requires_grad=False)
+            self.SCB = scb
+            self.quant_state = [scb, torch.Size(shape), w.dtype, None, None, "int8", None]
+            if self.bias is not None and self.bias.dtype != torch.float16:
+                self.bias = nn.Parameter(self.bias.data.to(torch.float16), requires_grad=False)
+            self.tiled = None
+            return
         if self.quant_type == "int4":
             qweight, scales, qzeros, sz = K.quantize_int4(w, self.blocksize)
             self.scales, self.qzeros, self.sz = scales, qzeros, sz
@@ -121,6 +130,8 @@ class QLinear(nn.Module):
             raise B200Error("QLinear is not quantized yet")
         dtype = dtype or self.compute_dtype
         shape = self.quant_state[1]
+        if self.quant_type == "int8":
+            return K.dequantize_int8(self.weight.data, self.SCB, dtype)
         if self.quant_type == "int4":
             return K.dequantize_int4(self.weight.data, self.scales, self.qzeros, shape[1], self.blocksize, dtype)
         return K.dequantize_4bit(self.weight.data, self.absmax, shape, dtype, self.quant_type, self.blocksize)
@@ -139,7 +150,7 @@ class QLinear(nn.Module):
                 if self.double_quant:
                     self.quant_state[4][1][0] = self.quant_state[4][1][0].to(dev)
                     self.quant_state[4][1][1] = self.quant_state[4][1][1].to(dev)
-                for name in ("scales", "qzeros", "sz", "tiled", "absmax"):
+                for name in ("scales", "qzeros", "sz", "tiled", "absmax", "SCB"):
                     t = getattr(self, name)
                     if t is not None:
                         setattr(self, name, t.to(dev))
@@ -161,7 +172,7 @@ class QLinear(nn.Module):
                                   f"({self.out_features}, {self.in_features})")
                 return
             target = self.weight.device
-            self.quant_state, self.scales, self.qzeros, self.sz, self.tiled, self.absmax = None, None, None, None, None, None
+            self.quant_state, self.scales, self.qzeros, self.sz, self.tiled, self.absmax, self.SCB = None, None, None, None, None, None, None
             if target.type == "cuda":
                 self.weight = nn.Parameter(w.detach().to(target), requires_grad=False)
                 self.quantize_()
@@ -183,6 +194,12 @@ class QLinear(nn.Module):
             raise B200Error("QLinear.forward needs the module quantized on CUDA and a CUDA input; there is no CPU "
                             "fallback (move the model with fabric.setup_module / .to('cuda'))")
         in_dtype = x.dtype
+        if self.quant_type == "int8":  # LLM.int8() computes in fp16 (bitsandbytes casts other dtypes to fp16 too)
+            try:
+                y = K.linear_int8(x if in_dtype == torch.float16 else x.to(torch.float16), self.weight.data, self.SCB, self.bias, self.threshold)
+            except NotImplementedError:  # in_features not a multiple of 64 (toy configs): dequantised fp16 product
+                y = F.linear(x.to(torch.float16), self.dequantize(torch.float16), self.bias)
+            return y if in_dtype == torch.float16 else y.to(in_dtype)
         if in_dtype != torch.bfloat16:
             x = x.to(torch.bfloat16)
         rows = x.numel() // self.in_features
@@ -197,6 +214,8 @@ class QLinear(nn.Module):
         """<= 16 activation rows through the fused dequant-GEMV: the streaming kernel over the tiled layout when the
         shape is covered (and the activation fits its shared memory), else the reference-layout kernel.
         ``other``: the up-projection for the fused SwiGLU pair (this module being the gate)."""
+        if self.quant_type == "int8":
+            raise B200Error("QLinear.gemv is the 4-bit fused path; int8 modules go through forward()")
         rows = x.numel() // self.in_features
         if self.tiled is not None and (other is None or other.tiled is not None) and rows * (2 * self.in_features + 16) <= 48 * 1024:
             try:
@@ -239,8 +258,12 @@ class QuantPrecision:
         if mode not in MODES:
             raise ValueError(f"Unsupported quantization mode {mode!r}; supported: {MODES}")
         self.mode = mode
-        self.dtype = dtype or torch.bfloat16
-        if self.dtype != torch.bfloat16:
+        self.dtype = dtype or (torch.float16 if mode == "int8" else torch.bfloat16)
+        if mode == "int8":
+            # tutorials/quantize.md:111: bnb.int8 runs with --precision 16-true; bf16 activations are cast per call
+            if self.dtype not in (torch.float16, torch.bfloat16):
+                raise NotImplementedError(f"bnb.int8 computes in fp16 (requested {self.dtype}); use --precision 16-true")
+        elif self.dtype != torch.bfloat16:
             raise NotImplementedError(f"b200gpt computes in bf16 (requested {self.dtype}); use --precision bf16-true")
         self.ignore_modules = set(ignore_modules or ())
 
