@@ -119,6 +119,29 @@ int b200_untile_4bit(const void* tiled, int64_t N, int64_t K, int qtype, int blo
 /* Same contract as b200_qgemv (prologue / epilogues / rounding points), reading tiled matrices; no workspace.
  * `prefetch`/`prefetch_bytes` (optional): a range the kernel asks the L2 to fetch (cp.async.bulk.prefetch.L2) -
  * the weights of the NEXT kernel in the decode graph - so HBM stays busy across the kernel boundary. */
+/* Tensor-parallel hand-off fused into the GEMV (replaces the all_reduce hook of generate/tp.py:73-74 on the decode path;
+ * DESIGN.md §6).  PRODUCER = the row-parallel Linear (attn.proj, mlp.proj): its epilogue stores this rank's bf16 partial
+ * into slot `rank` of EVERY rank's buffer over NVLink peer memory; when the launch's last CTA is done it raises this
+ * rank's arrival flag on every rank.  CONSUMER = the next Linear (whose `delta` the all-reduced tensor would have been):
+ * its prologue waits for the `world` local flags, adds the slots in rank order in fp32, rounds once to bf16 and carries
+ * on as with `delta`; its last CTA lowers the flags.  Consecutive hand-offs must alternate between two buffers.  All
+ * counters and flags are uint32 and zero before first use.  Pointers come from b200_p2p_alloc / b200_p2p_open. */
+typedef struct b200_tp_handoff {
+  int world, rank;
+  void* peer_y[8];        /* producer: slot `rank` (batch, N) bf16 in the buffer of rank r, own rank included */
+  void* peer_flag[8];     /* producer: arrival flag of `rank` in the buffer of rank r */
+  void* send_done;        /* producer: local CTA counter; NULL = this launch is not a producer */
+  const void* slots;      /* consumer: local slots, rank r at slots + r * slot_stride bytes; NULL = not a consumer */
+  int64_t slot_stride;
+  void* flags;            /* consumer: local arrival flags uint32[world] */
+  void* recv_done;        /* consumer: local CTA counter */
+} b200_tp_handoff;
+/* Symmetric peer buffers (setup time, not per token): cudaMalloc + zero + IPC export / import / release. */
+int b200_p2p_alloc(size_t bytes, void** ptr, void* handle64);
+int b200_p2p_open(const void* handle64, void** ptr);
+int b200_p2p_close(void* ptr);
+int b200_p2p_free(void* ptr);
+
 typedef struct b200_qgemv_tiled_args {
   const void* tiled;
   const void* tiled2;      /* second matrix for SWIGLU, else NULL */
@@ -141,6 +164,7 @@ typedef struct b200_qgemv_tiled_args {
   void* workspace;         /* zero-initialised once by the caller, >= b200_qgemv_tiled_workspace_bytes(); holds the
                               partial sums / arrival counters of row pairs cut by a stream-K boundary (self-cleaning) */
   size_t workspace_bytes;
+  const struct b200_tp_handoff* tp; /* optional tensor-parallel hand-off (below); NULL on one GPU */
 } b200_qgemv_tiled_args;
 size_t b200_qgemv_tiled_workspace_bytes(void);
 int b200_qgemv_tiled(const b200_qgemv_tiled_args* args, b200_stream_t stream);

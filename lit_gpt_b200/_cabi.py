@@ -36,6 +36,11 @@ class QGemvArgs(ctypes.Structure):
     ]
 
 
+class TpHandoff(ctypes.Structure):  # mirrors b200_tp_handoff
+    _fields_ = [("world", c_int), ("rank", c_int), ("peer_y", c_void_p * 8), ("peer_flag", c_void_p * 8), ("send_done", c_void_p),
+                ("slots", c_void_p), ("slot_stride", c_int64), ("flags", c_void_p), ("recv_done", c_void_p)]
+
+
 class QGemvTiledArgs(ctypes.Structure):
     _fields_ = [
         ("tiled", c_void_p), ("tiled2", c_void_p), ("qtype", c_int), ("blocksize", c_int), ("N", c_int64), ("K", c_int64),
@@ -43,6 +48,7 @@ class QGemvTiledArgs(ctypes.Structure):
         ("norm_eps", c_float), ("batch", c_int), ("epilogue", c_int),
         ("bias", c_void_p), ("bias2", c_void_p), ("residual", c_void_p), ("y", c_void_p),
         ("prefetch", c_void_p), ("prefetch_bytes", c_int64), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+        ("tp", ctypes.POINTER(TpHandoff)),
     ]
 
 
@@ -94,6 +100,10 @@ _SIGNATURES = {
     "b200_quantize_4bit": (c_int, [c_void_p, c_int, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "b200_dequantize_4bit": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int, c_void_p]),
     "b200_double_quant_absmax": (c_int, [c_void_p, c_int64, c_void_p, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "b200_p2p_alloc": (c_int, [c_size_t, ctypes.POINTER(c_void_p), c_void_p]),
+    "b200_p2p_open": (c_int, [c_void_p, ctypes.POINTER(c_void_p)]),
+    "b200_p2p_close": (c_int, [c_void_p]),
+    "b200_p2p_free": (c_int, [c_void_p]),
     "b200_quantize_int8": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "b200_dequantize_int8": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int, c_void_p]),
     "b200_linear_int8_workspace_bytes": (c_size_t, [c_int64, c_int64]),

@@ -46,6 +46,15 @@ struct StreamParams {
   int debug;           // 1: consumers skip the dequant/MMA work (streaming ceiling measurement only)
   const uint8_t* pf;   // L2 prefetch range (next kernel's weights), may be null
   int64_t pf_bytes;
+  // tensor-parallel hand-off over peer memory (b200_tp_handoff)
+  int tp_world;
+  __nv_bfloat16* tp_peer_y[8];   // producer: this rank's partial goes here on every rank
+  uint32_t* tp_peer_flag[8];     // producer: arrival flag of this rank on every rank
+  uint32_t* tp_send_done;        // producer: local CTA counter
+  const __nv_bfloat16* tp_slots; // consumer: local slots (the partial of rank r at + r * tp_slot_stride elements)
+  int64_t tp_slot_stride;
+  uint32_t* tp_flags;            // consumer: local arrival flags [world]
+  uint32_t* tp_recv_done;        // consumer: local CTA counter
 };
 
 constexpr int kSThreads = 256;
@@ -226,14 +235,38 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   griddep_launch();
   griddep_wait();
 
+  // ---- tensor-parallel consumer: the branch output is the sum of every rank's partial, written into this rank's
+  // slots by the peers' epilogues (and its own); wait until each rank's arrival flag is up
+  if (p.tp_slots) {
+    if (tid < p.tp_world) {
+      const long long t0 = clock64();
+      uint32_t f;
+      do {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(f) : "l"(p.tp_flags + tid) : "memory");
+        if (f == 0 && clock64() - t0 > 8000000000LL) __trap();  // a peer died: fail loudly instead of hanging the GPU
+      } while (f == 0);
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+  }
   // ---- activation prologue: (x + delta) -> optional RMSNorm -> bf16 rows in shared memory ---------------------
   const bool designated = blockIdx.x == 0;
   for (int b = 0; b < B; ++b) {
     float ss = 0.f;
     for (int c = tid; c < chunks; c += kConsumers) {
       uint4 v = *reinterpret_cast<const uint4*>(p.x + (int64_t)b * p.K + c * 8);
-      if (p.delta) {
-        const uint4 dv = *reinterpret_cast<const uint4*>(p.delta + (int64_t)b * p.K + c * 8);
+      if (p.delta || p.tp_slots) {
+        uint4 dv;
+        if (p.tp_slots) {  // sum of the ranks' partials in rank order (fp32), rounded once to bf16 like an all-reduced tensor
+          float acc8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          for (int r = 0; r < p.tp_world; ++r) {
+            const uint4 pv = __ldcg(reinterpret_cast<const uint4*>(p.tp_slots + r * p.tp_slot_stride + (int64_t)b * p.K + c * 8));
+            acc8[0] += bf16lo(pv.x); acc8[1] += bf16hi(pv.x); acc8[2] += bf16lo(pv.y); acc8[3] += bf16hi(pv.y);
+            acc8[4] += bf16lo(pv.z); acc8[5] += bf16hi(pv.z); acc8[6] += bf16lo(pv.w); acc8[7] += bf16hi(pv.w);
+          }
+          dv = make_uint4(pack_bf16(acc8[0], acc8[1]), pack_bf16(acc8[2], acc8[3]), pack_bf16(acc8[4], acc8[5]), pack_bf16(acc8[6], acc8[7]));
+        } else {
+          dv = *reinterpret_cast<const uint4*>(p.delta + (int64_t)b * p.K + c * 8);
+        }
         v.x = pack_bf16(bf16lo(v.x) + bf16lo(dv.x), bf16hi(v.x) + bf16hi(dv.x));
         v.y = pack_bf16(bf16lo(v.y) + bf16lo(dv.y), bf16hi(v.y) + bf16hi(dv.y));
         v.z = pack_bf16(bf16lo(v.z) + bf16lo(dv.z), bf16hi(v.z) + bf16hi(dv.z));
@@ -275,6 +308,13 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     }
   }
   asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");  // x_s and the LUT are published
+  if (p.tp_slots && tid == 0) {  // last CTA to have read the slots lowers the flags for the next use of this buffer
+    const uint32_t old = atomicAdd(p.tp_recv_done, 1u);
+    if (old == gridDim.x - 1) {
+      for (int r = 0; r < p.tp_world; ++r) p.tp_flags[r] = 0u;
+      *p.tp_recv_done = 0u;
+    }
+  }
   if (INT4) {       // per (batch row, k-block) activation sums for the zero-point term
     for (int i = tid; i < B * p.nkb; i += kConsumers) {
       const int b = i / p.nkb, kb = i % p.nkb;
@@ -393,7 +433,11 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   auto store_out = [&](int64_t n, int c, float v) {  // STORE / RESIDUAL epilogues for one (row, batch column)
     float h = v + (p.bias ? __bfloat162float(p.bias[n]) : 0.f);
     if (p.epilogue == B200_EPI_RESIDUAL) h = round_bf16(h) + __bfloat162float(p.residual[(int64_t)c * p.N + n]);
-    p.y[(int64_t)c * p.N + n] = __float2bfloat16_rn(h);
+    const __nv_bfloat16 hb = __float2bfloat16_rn(h);
+    if (p.y) p.y[(int64_t)c * p.N + n] = hb;
+    if (p.tp_send_done) {  // row-parallel partial: straight into every rank's slot over NVLink
+      for (int r = 0; r < p.tp_world; ++r) p.tp_peer_y[r][(int64_t)c * p.N + n] = hb;
+    }
   };
 
 
@@ -489,6 +533,18 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
       ++it;
     }
     u = nu_; r = nr; has1 = nhas1;
+  }  if (p.tp_send_done) {
+    // every thread's peer stores are ordered before the CTA's arrival; the last CTA raises this rank's flag on every rank
+    __threadfence_system();
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+    if (tid == 0) {
+      const uint32_t old = atomicAdd(p.tp_send_done, 1u);
+      if (old == gridDim.x - 1) {
+        *p.tp_send_done = 0u;
+        __threadfence_system();
+        for (int r = 0; r < p.tp_world; ++r) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.tp_peer_flag[r]), "r"(1u) : "memory");
+      }
+    }
   }
 }
 
@@ -522,7 +578,7 @@ int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch) {
 
 int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   B200_CHECK_ARG(a != nullptr, "b200_qgemv_tiled: null args");
-  B200_CHECK_ARG(a->tiled && a->x && a->y, "b200_qgemv_tiled: null tiled/x/y pointer");
+  B200_CHECK_ARG(a->tiled && a->x && (a->y || (a->tp && a->tp->send_done)), "b200_qgemv_tiled: null tiled/x/y pointer");
   B200_CHECK_ARG(a->N > 0 && a->K > 0, "b200_qgemv_tiled: N and K must be positive (N=%lld K=%lld)", (long long)a->N, (long long)a->K);
   B200_CHECK_ARG(a->batch >= 1 && a->batch <= 16, "b200_qgemv_tiled: batch must be in [1,16] (got %d); use b200_qgemm for prefill", a->batch);
   B200_CHECK_ARG(a->qtype == B200_Q_NF4 || a->qtype == B200_Q_FP4 || a->qtype == B200_Q_INT4, "b200_qgemv_tiled: bad qtype %d", a->qtype);
@@ -557,6 +613,31 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   p.xstride = (int)a->K + 8;
   p.debug = g_stream_depth.load() == 99 ? 1 : 0;
   if (g_stream_pf.load() && a->prefetch && a->prefetch_bytes >= 16) { p.pf = reinterpret_cast<const uint8_t*>(a->prefetch); p.pf_bytes = a->prefetch_bytes; }
+
+  if (a->tp) {
+    const b200_tp_handoff* h = a->tp;
+    B200_CHECK_ARG(h->world >= 2 && h->world <= 8 && h->rank >= 0 && h->rank < h->world, "b200_qgemv_tiled: tp world %d / rank %d out of range", h->world, h->rank);
+    B200_CHECK_ARG(!(h->slots && a->delta), "b200_qgemv_tiled: tp slots replace delta (pass delta = NULL)");
+    B200_CHECK_ARG(!(h->send_done && swiglu), "b200_qgemv_tiled: the SWIGLU pair is column-parallel: nothing to hand off");
+    p.tp_world = h->world;
+    if (h->send_done) {
+      for (int r = 0; r < h->world; ++r) {
+        B200_CHECK_ARG(h->peer_y[r] && h->peer_flag[r], "b200_qgemv_tiled: tp producer needs peer_y / peer_flag for every rank");
+        p.tp_peer_y[r] = reinterpret_cast<__nv_bfloat16*>(h->peer_y[r]);
+        p.tp_peer_flag[r] = reinterpret_cast<uint32_t*>(h->peer_flag[r]);
+      }
+      p.tp_send_done = reinterpret_cast<uint32_t*>(h->send_done);
+    }
+    if (h->slots) {
+      B200_CHECK_ARG(h->flags && h->recv_done && h->slot_stride >= (int64_t)a->batch * a->K * 2 && h->slot_stride % 16 == 0 &&
+                         (reinterpret_cast<uintptr_t>(h->slots) & 15) == 0,
+                     "b200_qgemv_tiled: tp consumer needs flags, recv_done and 16-byte aligned slots of >= batch * K * 2 bytes");
+      p.tp_slots = reinterpret_cast<const __nv_bfloat16*>(h->slots);
+      p.tp_slot_stride = h->slot_stride / 2;
+      p.tp_flags = reinterpret_cast<uint32_t*>(h->flags);
+      p.tp_recv_done = reinterpret_cast<uint32_t*>(h->recv_done);
+    }
+  }
 
   const int NB = a->batch > 8 ? 2 : 1;
   const int COLS = 8 * NB;

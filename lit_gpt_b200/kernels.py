@@ -249,8 +249,10 @@ def qgemv_tiled(x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, quant_type
                 bias: Optional[torch.Tensor] = None, bias2: Optional[torch.Tensor] = None, delta: Optional[torch.Tensor] = None,
                 x_out: Optional[torch.Tensor] = None, norm_weight: Optional[torch.Tensor] = None, norm_eps: float = 1e-5,
                 residual: Optional[torch.Tensor] = None, tiled2: Optional[torch.Tensor] = None,
-                prefetch: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """y = epilogue(prologue(x) @ dequant(W).T) over tiled matrices; see b200_qgemv_tiled in include/b200gpt.h."""
+                prefetch: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                tp: Optional["C.TpHandoff"] = None) -> torch.Tensor:
+    """y = epilogue(prologue(x) @ dequant(W).T) over tiled matrices; see b200_qgemv_tiled in include/b200gpt.h.
+    ``tp``: tensor-parallel hand-off over peer memory (lit_gpt_b200/p2p.py builds it)."""
     C.require_cuda(x, tiled)
     x = _bf16c(x, "x")
     if x.shape[-1] != K:
@@ -267,7 +269,7 @@ def qgemv_tiled(x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, quant_type
         delta=C.ptr(delta), x_out=C.ptr(x_out), norm_weight=C.ptr(norm_weight), norm_eps=norm_eps, batch=batch, epilogue=epilogue,
         bias=C.ptr(bias), bias2=C.ptr(bias2), residual=C.ptr(residual), y=y.data_ptr(), prefetch=C.ptr(prefetch),
         prefetch_bytes=0 if prefetch is None else prefetch.numel() * prefetch.element_size(),
-        workspace=ws.data_ptr(), workspace_bytes=ws.numel())
+        workspace=ws.data_ptr(), workspace_bytes=ws.numel(), tp=None if tp is None else ctypes.pointer(tp))
     C.check(C.load().b200_qgemv_tiled(ctypes.byref(args), C.stream_ptr(x.device)), "qgemv_tiled")
     return y
 

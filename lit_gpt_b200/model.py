@@ -140,6 +140,7 @@ class GPT(nn.Module):
 
     def _apply(self, fn, recurse: bool = True):
         self._fused_plan = None  # device moves quantize the Linears: re-plan on the next forward
+        self.__dict__.pop("_p2p", None)
         self.__dict__.pop("_decode_programs", None)
         return super()._apply(fn, recurse)
 
@@ -185,6 +186,36 @@ class GPT(nn.Module):
 
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.tp_group)  # NCCL over NVLink; sums row-parallel partials
         return t
+
+    # ---- tensor-parallel hand-off over peer memory (lit_gpt_b200/p2p.py) instead of NCCL on the decode path ----------
+    def _tp_comm(self, batch: int) -> Optional[Any]:
+        """The peer-memory communicator of the fused decode step, created collectively on first use (never during graph
+        capture); None -> the NCCL all-reduce path (B200_TP_NCCL=1, non-tiled shapes, or peer mapping unavailable)."""
+        st = self.__dict__.get("_p2p")
+        if st is not None:
+            return st or None
+        if torch.cuda.is_current_stream_capturing():
+            return None
+        import os
+
+        from .p2p import PeerComm
+
+        blocks = list(self.transformer.h)
+        lins = [self.lm_head] + [l for b in blocks for l in (b.attn.attn, b.attn.proj, b.mlp.fc_1, b.mlp.fc_2, b.mlp.proj)]
+        ok = (os.environ.get("B200_TP_NCCL", "0") != "1" and all(l.tiled is not None for l in lins)
+              and all(16 * (2 * l.in_features + 16) <= 48 * 1024 or batch * (2 * l.in_features + 16) <= 48 * 1024 for l in lins))
+        comm: Any = False
+        if ok:
+            try:
+                d_full = blocks[0].attn.proj.out_features
+                comm = PeerComm(self.tp_group, self.transformer.wte.weight.device, 16 * d_full * 2)
+            except Exception as e:  # consistent on all ranks (PeerComm agrees on failure collectively)
+                import warnings
+
+                warnings.warn(f"peer-memory hand-off unavailable ({e}); tensor-parallel decode uses NCCL all-reduce")
+                comm = False
+        self.__dict__["_p2p"] = comm
+        return comm or None
 
     # ---- persistent decode step: the whole T = 1 forward as ONE kernel launch (csrc/decode_step.cu) ---------
     # Experimental (off by default): measured 2.1 ms/step vs 1.73 ms for the PDL-chained per-op launches on
@@ -264,6 +295,36 @@ class GPT(nn.Module):
             return q.gemv(inp, prefetch=None if nxt is None else nxt.tiled, **kw)
 
         blocks = list(self.transformer.h)
+        comm = self._tp_comm(B) if tp and B <= 16 else None
+        if comm is not None:
+            # TP over peer memory: the row-parallel GEMV's epilogue writes its partial into every rank's slot, the next
+            # GEMV's prologue sums the slots (b200_tp_handoff): no all-reduce launch, no NCCL on the decode path.
+            # Hand-offs alternate between buffer 0 (attention branch) and buffer 1 (MLP branch).
+            def tlin(q: QLinear, inp: torch.Tensor, other: Optional[QLinear] = None, send: Optional[int] = None,
+                     recv: Optional[int] = None, **kw: Any) -> torch.Tensor:
+                return K.qgemv_tiled(inp, q.tiled, q.out_features, q.in_features, q.quant_type, q.blocksize,
+                                     tiled2=None if other is None else other.tiled, tp=comm.handoff(send, recv), **kw)
+
+            for li, block in enumerate(blocks):
+                a, m, cache = block.attn, block.mlp, block.attn.kv_cache
+                if li == 0:
+                    qkv = lin(a.attn, x, norm_weight=block.norm_1.weight, norm_eps=eps)
+                else:
+                    x_new = torch.empty_like(x)
+                    qkv = tlin(a.attn, x, recv=1, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps)
+                    x = x_new
+                y = K.attn_decode(qkv, self.cos, self.sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups,
+                                  c.head_size, c.rope_n_elem)
+                tlin(a.proj, y, send=0)
+                x_new = torch.empty_like(x)
+                act = tlin(m.fc_1, x, other=m.fc_2, recv=0, x_out=x_new, norm_weight=block.norm_2.weight, norm_eps=eps)
+                x = x_new
+                tlin(m.proj, act, send=1)
+            if blocks:
+                logits = tlin(self.lm_head, x, recv=1, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+            else:
+                logits = lin(self.lm_head, x, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+            return logits.view(B, 1, -1)
         for li, block in enumerate(blocks):
             a, m, cache = block.attn, block.mlp, block.attn.kv_cache
             nxt_qkv = blocks[li + 1].attn.attn if li + 1 < len(blocks) else self.lm_head
