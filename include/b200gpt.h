@@ -211,6 +211,16 @@ int b200_rope_kv_append(const void* qkv, const void* cos, const void* sin, int t
                         int rope_n_elem, const void* pos, int pos_is_int64, void* k_cache, void* v_cache, void* q_out, int batch,
                         int T, int n_head, int n_groups, int head_size, int max_seq, b200_stream_t stream);
 
+/* ---- prefill attention (T > 1) over the GQA-native caches: replaces F.scaled_dot_product_attention at
+ * lit_gpt/model.py:658-665 for the cached multi-token call (model.py:646-650).  q is (batch, n_head, T, head_size),
+ * already roped (b200_rope_kv_append); query row t attends to cache positions j <= pos[t] (the mask row
+ * model.py:509 selects), so the caches must already hold positions up to max(pos).  fp32 online softmax.
+ * y is written as (batch, T, n_head * head_size), the layout attn.proj consumes (model.py:653).
+ * head_size 64 or 128. */
+int b200_attn_prefill(const void* q, const void* k_cache, const void* v_cache, const void* pos, int pos_is_int64, void* y,
+                      int batch, int T, int n_head, int n_groups, int head_size, int max_seq, float scale,
+                      b200_stream_t stream);
+
 /* ---- small glue kernels so a whole decode step is one CUDA graph of this library's kernels ---------------- */
 /* out[r, :] = wte[idx[r], :]  (lit_gpt/model.py:515) */
 int b200_embedding(const void* idx, int idx_is_int64, const void* wte, void* out, int64_t rows, int64_t dim,

@@ -126,6 +126,8 @@ _SIGNATURES = {
     "b200_attn_decode": (c_int, [ctypes.POINTER(AttnDecodeArgs), c_void_p]),
     "b200_rope_kv_append": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                     c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_attn_prefill": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                  c_float, c_void_p]),
     "b200_embedding": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p]),
     "b200_argmax": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int, c_void_p, c_int, c_void_p, c_int64, c_void_p]),
     "b200_qgemm_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64]),

@@ -397,6 +397,25 @@ def rope_kv_append(qkv: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, pos:
     return q
 
 
+def attn_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, pos: torch.Tensor, scale: Optional[float] = None) -> torch.Tensor:
+    """Prefill attention (reference ``scaled_dot_product_attention``, lit_gpt/model.py:658-665, cached call): q (B, H, T, hs)
+    roped, caches (B, G, Tmax, hs) already extended; row t sees cache positions <= pos[t].  Returns (B, T, H * hs)."""
+    C.require_cuda(q, k_cache, v_cache, pos)
+    q = _bf16c(q, "q")
+    if k_cache.dtype != torch.bfloat16 or v_cache.dtype != torch.bfloat16 or not (k_cache.is_contiguous() and v_cache.is_contiguous()):
+        raise C.B200Error("attn_prefill: caches must be contiguous bf16")
+    B, H, T, hs = q.shape
+    G, Tmax = k_cache.shape[1], k_cache.shape[2]
+    if pos.numel() != T:
+        raise C.B200Error("attn_prefill: pos must have one entry per token")
+    pos = pos.contiguous()
+    y = torch.empty((B, T, H * hs), dtype=torch.bfloat16, device=q.device)
+    C.check(C.load().b200_attn_prefill(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), pos.data_ptr(), int(pos.dtype == torch.int64),
+                                       y.data_ptr(), B, T, H, G, hs, Tmax, float(scale if scale is not None else hs ** -0.5),
+                                       C.stream_ptr(q.device)), "attn_prefill")
+    return y
+
+
 def set_pdl(enabled: bool) -> bool:
     return bool(C.load().b200_set_pdl(int(enabled)))
 

@@ -433,10 +433,8 @@ class CausalSelfAttention(nn.Module):
             return y.view(B, 1, c.n_head * c.head_size)
         q = K.rope_kv_append(qkv, cos, sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups, c.head_size,
                              c.rope_n_elem, table_preselected=True)
-        scale = 1.0 / math.sqrt(c.head_size)
-        y = F.scaled_dot_product_attention(q, cache.k, cache.v, attn_mask=mask, dropout_p=0.0, scale=scale,
-                                           enable_gqa=c.n_query_groups != c.n_head)
-        return y.transpose(1, 2).reshape(B, T, c.n_head * c.head_size)
+        # the mask row of token t (model.py:509) is "cache positions <= input_pos[t]": the kernel takes input_pos directly
+        return K.attn_prefill(q, cache.k, cache.v, input_pos, 1.0 / math.sqrt(c.head_size))
 
     def scaled_dot_product_attention(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
                                      mask: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -316,6 +316,42 @@ def test_rope_kv_append(K):
     assert kc[:, :, :3].abs().sum() == 0 and kc[:, :, 3 + T :].abs().sum() == 0
 
 
+@pytest.mark.parametrize("B,T,H,G,hs,start,max_seq", [
+    (1, 16, 8, 8, 128, 0, 64),        # MHA, one partial tile
+    (2, 200, 8, 2, 128, 0, 256),      # GQA, several key tiles, ragged last query tile
+    (1, 130, 4, 1, 64, 37, 300),      # MQA, head size 64 (pythia), chunked prefill starting at position 37
+    (1, 1, 4, 4, 128, 5, 16),         # single row through the prefill kernel
+    (1, 513, 2, 2, 128, 0, 513),      # cache exactly full
+])
+def test_attn_prefill_vs_oracle(K, B, T, H, G, hs, start, max_seq):
+    """Prefill attention against the reference formulation (lit_gpt/model.py:658-665: SDPA with the mask rows that
+    input_pos selects), computed in fp32 on the bf16 inputs.  Tolerance: bf16 output rounding (2^-8 relative) plus
+    the bf16 rounding of the probabilities fed to P.V, i.e. 2^-7 * max|v| absolute."""
+    g = torch.Generator().manual_seed(B * 1000 + T)
+    q = torch.randn(B, H, T, hs, generator=g).bfloat16()
+    kc = torch.zeros(B, G, max_seq, hs).bfloat16()
+    vc = torch.zeros(B, G, max_seq, hs).bfloat16()
+    filled = start + T
+    kc[:, :, :filled] = torch.randn(B, G, filled, hs, generator=g).bfloat16()
+    vc[:, :, :filled] = torch.randn(B, G, filled, hs, generator=g).bfloat16()
+    # garbage past the filled region must never be read (reference: masked out)
+    kc[:, :, filled:] = 1e4
+    vc[:, :, filled:] = 1e4
+    pos = torch.arange(start, start + T)
+    y = K.attn_prefill(q.cuda(), kc.cuda(), vc.cuda(), pos.cuda(), 1.0 / hs ** 0.5).float().cpu()
+    y32 = K.attn_prefill(q.cuda(), kc.cuda(), vc.cuda(), pos.to(torch.int32).cuda(), 1.0 / hs ** 0.5).float().cpu()
+    assert torch.equal(y, y32)
+    qpk = H // G
+    kf = kc.float().repeat_interleave(qpk, dim=1)
+    vf = vc.float().repeat_interleave(qpk, dim=1)
+    mask = torch.tril(torch.ones(max_seq, max_seq, dtype=torch.bool))[pos].view(1, 1, T, max_seq)   # model.py:509, 802-804
+    ref = torch.nn.functional.scaled_dot_product_attention(q.float(), kf, vf, attn_mask=mask, dropout_p=0.0, scale=1.0 / hs ** 0.5)
+    ref = ref.transpose(1, 2).reshape(B, T, H * hs)
+    err = (y - ref).abs().max().item()
+    tol = 2.0 ** -7 * vc[:, :, :filled].float().abs().max().item()
+    assert err <= tol, (err, tol)
+
+
 # ---------------------------------------------------------------------------------------------------------
 # tiled layout + streaming GEMV (the decode hot path)
 # ---------------------------------------------------------------------------------------------------------
