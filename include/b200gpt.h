@@ -120,20 +120,23 @@ int b200_untile_4bit(const void* tiled, int64_t N, int64_t K, int qtype, int blo
  * `prefetch`/`prefetch_bytes` (optional): a range the kernel asks the L2 to fetch (cp.async.bulk.prefetch.L2) -
  * the weights of the NEXT kernel in the decode graph - so HBM stays busy across the kernel boundary. */
 /* Tensor-parallel hand-off fused into the GEMV (replaces the all_reduce hook of generate/tp.py:73-74 on the decode path;
- * DESIGN.md §6).  PRODUCER = the row-parallel Linear (attn.proj, mlp.proj): its epilogue stores this rank's bf16 partial
- * into slot `rank` of EVERY rank's buffer over NVLink peer memory; when the launch's last CTA is done it raises this
- * rank's arrival flag on every rank.  CONSUMER = the next Linear (whose `delta` the all-reduced tensor would have been):
- * its prologue waits for the `world` local flags, adds the slots in rank order in fp32, rounds once to bf16 and carries
- * on as with `delta`; its last CTA lowers the flags.  Consecutive hand-offs must alternate between two buffers.  All
- * counters and flags are uint32 and zero before first use.  Pointers come from b200_p2p_alloc / b200_p2p_open. */
+ * DESIGN.md §6).  PRODUCER = the row-parallel Linear (attn.proj, mlp.proj): its epilogue stores this rank's partial
+ * into slot `rank` of EVERY rank's buffer over NVLink peer memory as self-validating 32-bit packets
+ * `tag << 16 | bf16 bits` (one store per output element, no fence, no separate flag: the "LL" scheme).
+ * CONSUMER = the next Linear (whose `delta` the all-reduced tensor would have been): its prologue polls the `world`
+ * local slots until every packet carries the expected tag, adds them in rank order in fp32, rounds once to bf16 and
+ * carries on as with `delta`; its last CTA bumps the buffer's sequence counter.  tag = seq % 65535 + 1, where seq is
+ * the buffer's LOCAL counter (all ranks run the same launch sequence, so the counters stay in lock step).
+ * Consecutive hand-offs must alternate between two buffers.  Counters are uint32 and zero before first use, slots are
+ * zero before first use.  Pointers come from b200_p2p_alloc / b200_p2p_open. */
 typedef struct b200_tp_handoff {
   int world, rank;
-  void* peer_y[8];        /* producer: slot `rank` (batch, N) bf16 in the buffer of rank r, own rank included */
-  void* peer_flag[8];     /* producer: arrival flag of `rank` in the buffer of rank r */
-  void* send_done;        /* producer: local CTA counter; NULL = this launch is not a producer */
+  void* peer_y[8];        /* producer: slot `rank` (batch, N) uint32 packets in the buffer of rank r, own rank included */
+  void* reserved[8];      /* must be NULL */
+  void* send_seq;         /* producer: LOCAL sequence counter of the buffer written; NULL = this launch is not a producer */
   const void* slots;      /* consumer: local slots, rank r at slots + r * slot_stride bytes; NULL = not a consumer */
-  int64_t slot_stride;
-  void* flags;            /* consumer: local arrival flags uint32[world] */
+  int64_t slot_stride;    /* >= batch * K * 4 bytes */
+  void* recv_seq;         /* consumer: LOCAL sequence counter of the buffer read (bumped by the launch's last CTA) */
   void* recv_done;        /* consumer: local CTA counter */
 } b200_tp_handoff;
 /* Symmetric peer buffers (setup time, not per token): cudaMalloc + zero + IPC export / import / release. */

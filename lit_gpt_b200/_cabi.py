@@ -37,8 +37,8 @@ class QGemvArgs(ctypes.Structure):
 
 
 class TpHandoff(ctypes.Structure):  # mirrors b200_tp_handoff
-    _fields_ = [("world", c_int), ("rank", c_int), ("peer_y", c_void_p * 8), ("peer_flag", c_void_p * 8), ("send_done", c_void_p),
-                ("slots", c_void_p), ("slot_stride", c_int64), ("flags", c_void_p), ("recv_done", c_void_p)]
+    _fields_ = [("world", c_int), ("rank", c_int), ("peer_y", c_void_p * 8), ("reserved", c_void_p * 8), ("send_seq", c_void_p),
+                ("slots", c_void_p), ("slot_stride", c_int64), ("recv_seq", c_void_p), ("recv_done", c_void_p)]
 
 
 class QGemvTiledArgs(ctypes.Structure):

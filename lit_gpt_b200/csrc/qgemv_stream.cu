@@ -46,14 +46,13 @@ struct StreamParams {
   int debug;           // 1: consumers skip the dequant/MMA work (streaming ceiling measurement only)
   const uint8_t* pf;   // L2 prefetch range (next kernel's weights), may be null
   int64_t pf_bytes;
-  // tensor-parallel hand-off over peer memory (b200_tp_handoff)
+  // tensor-parallel hand-off over peer memory (b200_tp_handoff): 32-bit packets tag << 16 | bf16
   int tp_world;
-  __nv_bfloat16* tp_peer_y[8];   // producer: this rank's partial goes here on every rank
-  uint32_t* tp_peer_flag[8];     // producer: arrival flag of this rank on every rank
-  uint32_t* tp_send_done;        // producer: local CTA counter
-  const __nv_bfloat16* tp_slots; // consumer: local slots (the partial of rank r at + r * tp_slot_stride elements)
+  uint32_t* tp_peer_y[8];        // producer: this rank's slot on every rank
+  const uint32_t* tp_send_seq;   // producer: local sequence counter of the buffer written
+  const uint32_t* tp_slots;      // consumer: local slots (rank r at + r * tp_slot_stride packets)
   int64_t tp_slot_stride;
-  uint32_t* tp_flags;            // consumer: local arrival flags [world]
+  uint32_t* tp_recv_seq;         // consumer: local sequence counter of the buffer read
   uint32_t* tp_recv_done;        // consumer: local CTA counter
 };
 
@@ -236,18 +235,10 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   griddep_wait();
 
   // ---- tensor-parallel consumer: the branch output is the sum of every rank's partial, written into this rank's
-  // slots by the peers' epilogues (and its own); wait until each rank's arrival flag is up
-  if (p.tp_slots) {
-    if (tid < p.tp_world) {
-      const long long t0 = clock64();
-      uint32_t f;
-      do {
-        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(f) : "l"(p.tp_flags + tid) : "memory");
-        if (f == 0 && clock64() - t0 > 8000000000LL) __trap();  // a peer died: fail loudly instead of hanging the GPU
-      } while (f == 0);
-    }
-    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
-  }
+  // slots by the peers' epilogues (and its own) as self-validating packets; the expected tag comes from the buffer's
+  // local sequence counter (last bumped at least two launches ago)
+  uint32_t rtag = 0;
+  if (p.tp_slots) rtag = (__ldcg(p.tp_recv_seq) % 65535u) + 1u;
   // ---- activation prologue: (x + delta) -> optional RMSNorm -> bf16 rows in shared memory ---------------------
   const bool designated = blockIdx.x == 0;
   for (int b = 0; b < B; ++b) {
@@ -259,9 +250,19 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
         if (p.tp_slots) {  // sum of the ranks' partials in rank order (fp32), rounded once to bf16 like an all-reduced tensor
           float acc8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
           for (int r = 0; r < p.tp_world; ++r) {
-            const uint4 pv = __ldcg(reinterpret_cast<const uint4*>(p.tp_slots + r * p.tp_slot_stride + (int64_t)b * p.K + c * 8));
-            acc8[0] += bf16lo(pv.x); acc8[1] += bf16hi(pv.x); acc8[2] += bf16lo(pv.y); acc8[3] += bf16hi(pv.y);
-            acc8[4] += bf16lo(pv.z); acc8[5] += bf16hi(pv.z); acc8[6] += bf16lo(pv.w); acc8[7] += bf16hi(pv.w);
+            const uint32_t* sp = p.tp_slots + r * p.tp_slot_stride + (int64_t)b * p.K + c * 8;
+            uint4 pa, pb;
+            const long long t0 = clock64();
+            for (;;) {   // poll until all eight packets carry this hand-off's tag
+              asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(pa.x), "=r"(pa.y), "=r"(pa.z), "=r"(pa.w) : "l"(sp) : "memory");
+              asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(pb.x), "=r"(pb.y), "=r"(pb.z), "=r"(pb.w) : "l"(sp + 4) : "memory");
+              const bool ok = (pa.x >> 16) == rtag && (pa.y >> 16) == rtag && (pa.z >> 16) == rtag && (pa.w >> 16) == rtag &&
+                              (pb.x >> 16) == rtag && (pb.y >> 16) == rtag && (pb.z >> 16) == rtag && (pb.w >> 16) == rtag;
+              if (ok) break;
+              if (clock64() - t0 > 8000000000LL) __trap();  // a peer died: fail loudly instead of hanging the GPU
+            }
+            acc8[0] += bf16lo(pa.x); acc8[1] += bf16lo(pa.y); acc8[2] += bf16lo(pa.z); acc8[3] += bf16lo(pa.w);
+            acc8[4] += bf16lo(pb.x); acc8[5] += bf16lo(pb.y); acc8[6] += bf16lo(pb.z); acc8[7] += bf16lo(pb.w);
           }
           dv = make_uint4(pack_bf16(acc8[0], acc8[1]), pack_bf16(acc8[2], acc8[3]), pack_bf16(acc8[4], acc8[5]), pack_bf16(acc8[6], acc8[7]));
         } else {
@@ -308,11 +309,11 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     }
   }
   asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");  // x_s and the LUT are published
-  if (p.tp_slots && tid == 0) {  // last CTA to have read the slots lowers the flags for the next use of this buffer
+  if (p.tp_slots && tid == 0) {  // last CTA to have read the slots bumps the buffer's sequence counter for its next use
     const uint32_t old = atomicAdd(p.tp_recv_done, 1u);
     if (old == gridDim.x - 1) {
-      for (int r = 0; r < p.tp_world; ++r) p.tp_flags[r] = 0u;
       *p.tp_recv_done = 0u;
+      *p.tp_recv_seq = __ldcg(p.tp_recv_seq) + 1u;
     }
   }
   if (INT4) {       // per (batch row, k-block) activation sums for the zero-point term
@@ -430,13 +431,16 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     }
   };
 
+  const uint32_t stag = p.tp_send_seq ? (__ldcg(p.tp_send_seq) % 65535u) + 1u : 0u;  // after griddep_wait: last bumped >= 2 launches ago
   auto store_out = [&](int64_t n, int c, float v) {  // STORE / RESIDUAL epilogues for one (row, batch column)
     float h = v + (p.bias ? __bfloat162float(p.bias[n]) : 0.f);
     if (p.epilogue == B200_EPI_RESIDUAL) h = round_bf16(h) + __bfloat162float(p.residual[(int64_t)c * p.N + n]);
     const __nv_bfloat16 hb = __float2bfloat16_rn(h);
     if (p.y) p.y[(int64_t)c * p.N + n] = hb;
-    if (p.tp_send_done) {  // row-parallel partial: straight into every rank's slot over NVLink
-      for (int r = 0; r < p.tp_world; ++r) p.tp_peer_y[r][(int64_t)c * p.N + n] = hb;
+    if (p.tp_send_seq) {  // row-parallel partial: one self-validating packet straight into every rank's slot over NVLink
+      const uint32_t pk = (stag << 16) | (uint32_t)bf16_bits(h);
+      for (int r = 0; r < p.tp_world; ++r)
+        asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p.tp_peer_y[r] + (int64_t)c * p.N + n), "r"(pk) : "memory");
     }
   };
 
@@ -533,18 +537,6 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
       ++it;
     }
     u = nu_; r = nr; has1 = nhas1;
-  }  if (p.tp_send_done) {
-    // every thread's peer stores are ordered before the CTA's arrival; the last CTA raises this rank's flag on every rank
-    __threadfence_system();
-    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
-    if (tid == 0) {
-      const uint32_t old = atomicAdd(p.tp_send_done, 1u);
-      if (old == gridDim.x - 1) {
-        *p.tp_send_done = 0u;
-        __threadfence_system();
-        for (int r = 0; r < p.tp_world; ++r) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.tp_peer_flag[r]), "r"(1u) : "memory");
-      }
-    }
   }
 }
 
@@ -578,7 +570,7 @@ int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch) {
 
 int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   B200_CHECK_ARG(a != nullptr, "b200_qgemv_tiled: null args");
-  B200_CHECK_ARG(a->tiled && a->x && (a->y || (a->tp && a->tp->send_done)), "b200_qgemv_tiled: null tiled/x/y pointer");
+  B200_CHECK_ARG(a->tiled && a->x && (a->y || (a->tp && a->tp->send_seq)), "b200_qgemv_tiled: null tiled/x/y pointer");
   B200_CHECK_ARG(a->N > 0 && a->K > 0, "b200_qgemv_tiled: N and K must be positive (N=%lld K=%lld)", (long long)a->N, (long long)a->K);
   B200_CHECK_ARG(a->batch >= 1 && a->batch <= 16, "b200_qgemv_tiled: batch must be in [1,16] (got %d); use b200_qgemm for prefill", a->batch);
   B200_CHECK_ARG(a->qtype == B200_Q_NF4 || a->qtype == B200_Q_FP4 || a->qtype == B200_Q_INT4, "b200_qgemv_tiled: bad qtype %d", a->qtype);
@@ -618,23 +610,22 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
     const b200_tp_handoff* h = a->tp;
     B200_CHECK_ARG(h->world >= 2 && h->world <= 8 && h->rank >= 0 && h->rank < h->world, "b200_qgemv_tiled: tp world %d / rank %d out of range", h->world, h->rank);
     B200_CHECK_ARG(!(h->slots && a->delta), "b200_qgemv_tiled: tp slots replace delta (pass delta = NULL)");
-    B200_CHECK_ARG(!(h->send_done && swiglu), "b200_qgemv_tiled: the SWIGLU pair is column-parallel: nothing to hand off");
+    B200_CHECK_ARG(!(h->send_seq && swiglu), "b200_qgemv_tiled: the SWIGLU pair is column-parallel: nothing to hand off");
     p.tp_world = h->world;
-    if (h->send_done) {
+    if (h->send_seq) {
       for (int r = 0; r < h->world; ++r) {
-        B200_CHECK_ARG(h->peer_y[r] && h->peer_flag[r], "b200_qgemv_tiled: tp producer needs peer_y / peer_flag for every rank");
-        p.tp_peer_y[r] = reinterpret_cast<__nv_bfloat16*>(h->peer_y[r]);
-        p.tp_peer_flag[r] = reinterpret_cast<uint32_t*>(h->peer_flag[r]);
+        B200_CHECK_ARG(h->peer_y[r] && (reinterpret_cast<uintptr_t>(h->peer_y[r]) & 3) == 0, "b200_qgemv_tiled: tp producer needs a 4-byte aligned peer_y for every rank");
+        p.tp_peer_y[r] = reinterpret_cast<uint32_t*>(h->peer_y[r]);
       }
-      p.tp_send_done = reinterpret_cast<uint32_t*>(h->send_done);
+      p.tp_send_seq = reinterpret_cast<const uint32_t*>(h->send_seq);
     }
     if (h->slots) {
-      B200_CHECK_ARG(h->flags && h->recv_done && h->slot_stride >= (int64_t)a->batch * a->K * 2 && h->slot_stride % 16 == 0 &&
+      B200_CHECK_ARG(h->recv_seq && h->recv_done && h->slot_stride >= (int64_t)a->batch * a->K * 4 && h->slot_stride % 16 == 0 &&
                          (reinterpret_cast<uintptr_t>(h->slots) & 15) == 0,
-                     "b200_qgemv_tiled: tp consumer needs flags, recv_done and 16-byte aligned slots of >= batch * K * 2 bytes");
-      p.tp_slots = reinterpret_cast<const __nv_bfloat16*>(h->slots);
-      p.tp_slot_stride = h->slot_stride / 2;
-      p.tp_flags = reinterpret_cast<uint32_t*>(h->flags);
+                     "b200_qgemv_tiled: tp consumer needs recv_seq, recv_done and 16-byte aligned slots of >= batch * K * 4 bytes");
+      p.tp_slots = reinterpret_cast<const uint32_t*>(h->slots);
+      p.tp_slot_stride = h->slot_stride / 4;
+      p.tp_recv_seq = reinterpret_cast<uint32_t*>(h->recv_seq);
       p.tp_recv_done = reinterpret_cast<uint32_t*>(h->recv_done);
     }
   }

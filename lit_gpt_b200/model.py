@@ -208,7 +208,7 @@ class GPT(nn.Module):
         if ok:
             try:
                 d_full = blocks[0].attn.proj.out_features
-                comm = PeerComm(self.tp_group, self.transformer.wte.weight.device, 16 * d_full * 2)
+                comm = PeerComm(self.tp_group, self.transformer.wte.weight.device, 16 * d_full * 4)  # 32-bit packets
             except Exception as e:  # consistent on all ranks (PeerComm agrees on failure collectively)
                 import warnings
 

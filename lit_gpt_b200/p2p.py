@@ -8,8 +8,10 @@ the symmetric buffers: allocation through the library (cudaMalloc + CUDA IPC), h
 ``torch.distributed`` group, and the per-launch ``TpHandoff`` descriptors.
 
 Buffer layout per rank:  [2 hand-off buffers][world slots][slot_bytes]  then, per buffer, 128 bytes of
-``uint32 flags[8] | recv_done | send_done``.  Consecutive hand-offs alternate between the two buffers (attention
-branch: 0, MLP branch: 1), which is what makes lowering the flags in the consumer race-free.
+``uint32 seq | .. | recv_done (+32)``.  A slot holds one 32-bit packet ``tag << 16 | bf16`` per element (the tag makes the
+packet self-validating: no fence and no separate arrival flag).  Consecutive hand-offs alternate between the two buffers
+(attention branch: 0, MLP branch: 1): a rank can only overwrite a peer's slot of buffer b after that peer has produced
+the next hand-off on the other buffer, i.e. after it has finished reading buffer b.
 """
 from __future__ import annotations
 
@@ -88,12 +90,11 @@ class PeerComm:
         if send is not None:
             for r in range(self.world):
                 h.peer_y[r] = self._slot(self.base[r], send, self.rank)
-                h.peer_flag[r] = self._flags(self.base[r], send) + 4 * self.rank
-            h.send_done = self._flags(self._local, send) + 36
+            h.send_seq = self._flags(self._local, send)
         if recv is not None:
             h.slots = self._slot(self._local, recv, 0)
             h.slot_stride = self.slot_bytes
-            h.flags = self._flags(self._local, recv)
+            h.recv_seq = self._flags(self._local, recv)
             h.recv_done = self._flags(self._local, recv) + 32
         return h
 
