@@ -28,6 +28,10 @@ struct AttnParams {
   float scale_log2;
 };
 
+// grouped-query kernel on mma.sync (attn_decode_gqa.cu)
+bool attn_decode_gqa_supported(int head_size, int qpk);
+cudaError_t launch_attn_decode_gqa(const AttnParams& p, dim3 grid, cudaStream_t st);
+
 __device__ __forceinline__ float table_at(const void* tab, int is_bf16, int64_t i) {
   return is_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(tab)[i]) : reinterpret_cast<const float*>(tab)[i];
 }
@@ -270,19 +274,40 @@ __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<H
   sync();
   if (!s_last) return;
   __threadfence();
-  for (int h = 0; h < nh; ++h) {
+  // (m, l) of every (head, split) staged in shared memory (s_acc is free again), converted in place to the split's
+  // weight exp2(m_s - m) / l_total; then one (head, dim) pair per thread with the split loads four deep in flight
+  float* s_w = &s_acc[0][0][0];                  // [nh][nsplit] weights   (nsplit <= 64: 8 * 64 * 2 floats fit easily)
+  float* s_mraw = s_w + QPK * 64;
+  const int NS = p.nsplit;
+  for (int i = tid; i < nh * NS; i += 128) {
+    const int h = i / NS, sp = i % NS;
+    const float* ml = p.ws_ml + (((int64_t)b * H + gi * p.qpk + h0 + h) * NS + sp) * 2;
+    s_mraw[i] = __ldcg(ml);
+    s_w[i] = __ldcg(ml + 1);
+  }
+  sync();
+  if (tid < nh) {
+    float mn = -INFINITY, lt = 0.f;
+    for (int sp = 0; sp < NS; ++sp) mn = fmaxf(mn, s_mraw[tid * NS + sp]);
+    for (int sp = 0; sp < NS; ++sp) lt += s_w[tid * NS + sp] * exp2f(s_mraw[tid * NS + sp] - mn);
+    const float inv = 1.f / lt;
+    for (int sp = 0; sp < NS; ++sp) s_w[tid * NS + sp] = exp2f(s_mraw[tid * NS + sp] - mn) * inv;
+  }
+  sync();
+  for (int i = tid; i < nh * HS; i += 128) {
+    const int h = i / HS, d = i % HS;
     const int head = gi * p.qpk + h0 + h;
-    const float* ml = p.ws_ml + ((int64_t)b * H + head) * p.nsplit * 2;
-    float mn = -INFINITY;
-    for (int s = 0; s < p.nsplit; ++s) mn = fmaxf(mn, __ldcg(ml + 2 * s));
-    float lt = 0.f;
-    for (int s = 0; s < p.nsplit; ++s) lt += __ldcg(ml + 2 * s + 1) * exp2f(__ldcg(ml + 2 * s) - mn);
-    for (int d = tid; d < HS; d += 128) {
-      float a = 0.f;
-      for (int s = 0; s < p.nsplit; ++s)
-        a += __ldcg(p.ws_acc + (((int64_t)b * H + head) * p.nsplit + s) * HS + d) * exp2f(__ldcg(ml + 2 * s) - mn);
-      p.out[((int64_t)b * H + head) * HS + d] = __float2bfloat16_rn(a / lt);
+    const float* src = p.ws_acc + ((int64_t)b * H + head) * NS * HS + d;
+    const float* w = s_w + h * NS;
+    float a = 0.f;
+    int sp = 0;
+    for (; sp + 4 <= NS; sp += 4) {
+      const float v0 = __ldcg(src + (int64_t)sp * HS), v1 = __ldcg(src + (int64_t)(sp + 1) * HS);
+      const float v2 = __ldcg(src + (int64_t)(sp + 2) * HS), v3 = __ldcg(src + (int64_t)(sp + 3) * HS);
+      a = fmaf(v0, w[sp], a); a = fmaf(v1, w[sp + 1], a); a = fmaf(v2, w[sp + 2], a); a = fmaf(v3, w[sp + 3], a);
     }
+    for (; sp < NS; ++sp) a = fmaf(__ldcg(src + (int64_t)sp * HS), w[sp], a);
+    p.out[((int64_t)b * H + head) * HS + d] = __float2bfloat16_rn(a);
   }
 }
 

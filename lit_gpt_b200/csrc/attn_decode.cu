@@ -66,7 +66,11 @@ static cudaError_t launch_attn(const AttnParams& p, int qpk_t, dim3 grid, cudaSt
 
 using namespace b200;
 
+static std::atomic<int> g_attn_force_scalar{0};
+
 extern "C" {
+
+int b200_attn_decode_tune(int force_scalar) { return g_attn_force_scalar.exchange(force_scalar ? 1 : 0); }
 
 size_t b200_attn_decode_workspace_bytes(int batch, int n_head, int head_size, int max_splits) {
   size_t acc = (size_t)batch * n_head * max_splits * head_size * sizeof(float);
@@ -88,12 +92,14 @@ int b200_attn_decode(const b200_attn_decode_args* a, b200_stream_t stream) {
   B200_CHECK_ARG(a->table_dtype == B200_F32 || a->table_dtype == B200_BF16, "b200_attn_decode: cos/sin must be fp32 or bf16");
   const int qpk = a->n_head / a->n_groups;
   const int qpk_t = qpk == 1 ? 1 : (qpk == 2 ? 2 : (qpk <= 4 ? 4 : 8));
-  const int head_chunks = (qpk + qpk_t - 1) / qpk_t;
+  // grouped / multi-query attention at head size 128: the heads of a group are the M rows of a tensor-core tile
+  const bool gqa = attn_decode_gqa_supported(a->head_size, qpk) && !g_attn_force_scalar.load(std::memory_order_relaxed);
+  const int head_chunks = gqa ? 1 : (qpk + qpk_t - 1) / qpk_t;
   int nsplit = a->num_splits;
   if (nsplit <= 0) {
     const int ctas = a->batch * a->n_groups * head_chunks;
-    nsplit = (2 * sm_count() + ctas - 1) / ctas;
-    const int by_len = (a->max_seq + 63) / 64;
+    nsplit = ((gqa ? 1 : 2) * sm_count() + ctas - 1) / ctas;
+    const int by_len = gqa ? (a->max_seq + 255) / 256 : (a->max_seq + 63) / 64;   // two 32-key tiles per warp at least
     if (nsplit > by_len) nsplit = by_len;
   }
   if (nsplit > 64) nsplit = 64;
@@ -119,7 +125,8 @@ int b200_attn_decode(const b200_attn_decode_args* a, b200_stream_t stream) {
   }
   p.scale_log2 = (1.0f / sqrtf((float)a->head_size)) * 1.4426950408889634f;
   dim3 grid(nsplit, a->n_groups * head_chunks, a->batch);
-  cudaError_t e = a->head_size == 128 ? launch_attn<128>(p, qpk_t, grid, (cudaStream_t)stream) : launch_attn<64>(p, qpk_t, grid, (cudaStream_t)stream);
+  cudaError_t e = gqa ? launch_attn_decode_gqa(p, grid, (cudaStream_t)stream)
+                      : (a->head_size == 128 ? launch_attn<128>(p, qpk_t, grid, (cudaStream_t)stream) : launch_attn<64>(p, qpk_t, grid, (cudaStream_t)stream));
   if (e != cudaSuccess) {
     set_error("b200_attn_decode: launch failed: %s", cudaGetErrorString(e));
     return B200_ERR_CUDA;

@@ -11,7 +11,7 @@
 // memory by cp.async; S = Q K^T and O += P V on mma.sync.m16n8k16 (bf16 -> fp32) with ldmatrix operand loads from
 // XOR-swizzled tiles.  The heads of one query group run in adjacent CTAs so the K/V tiles are shared through L2.
 // Output is written as (B, T, H * hs), the layout attn.proj consumes (model.py:653).
-#include "common.cuh"
+#include "mma_tile.cuh"
 
 namespace b200 {
 
@@ -20,30 +20,6 @@ namespace {
 constexpr int kPfBM = 128;   // query rows per CTA
 constexpr int kPfBN = 64;    // keys per tile
 constexpr int kPfThreads = 256;
-
-__device__ __forceinline__ uint32_t pf_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void pf_cp16(uint32_t dst, const void* src, bool valid) {
-  const int sz = valid ? 16 : 0;  // zero-fill when out of range
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
-}
-__device__ __forceinline__ void pf_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void pf_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
-}
-__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
-}
-__device__ __forceinline__ void pf_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-
-// byte offset of 16-byte chunk `c` of row `r` in a tile with HS bf16 per row (chunk index XOR-swizzled by the row)
-template <int HS>
-__device__ __forceinline__ uint32_t sw(int r, int c) { return (uint32_t)(r * HS * 2 + ((c ^ (r & 7)) << 4)); }
 
 template <int HS, typename PosT>
 __global__ void __launch_bounds__(kPfThreads, 1)

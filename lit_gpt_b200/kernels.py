@@ -416,6 +416,11 @@ def attn_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
     return y
 
 
+def attn_decode_tune(force_scalar: bool = False) -> bool:
+    """Test knob: route grouped-query shapes through the scalar decode-attention kernel; returns the previous setting."""
+    return bool(C.load().b200_attn_decode_tune(int(force_scalar)))
+
+
 def set_pdl(enabled: bool) -> bool:
     return bool(C.load().b200_set_pdl(int(enabled)))
 

@@ -203,7 +203,10 @@ class QLinear(nn.Module):
         if in_dtype != torch.bfloat16:
             x = x.to(torch.bfloat16)
         rows = x.numel() // self.in_features
-        if rows <= GEMV_MAX_ROWS:
+        # <= 16 rows: the streaming GEMV, provided the activation rows fit its shared-memory plan (a 16-token prompt at
+        # K = 8192 does not: that call is a small prefill and takes the GEMM); shapes without a tiled layout (toy
+        # configs) keep the reference-layout GEMV
+        if rows <= GEMV_MAX_ROWS and (self.tiled is None or rows == 1 or rows * (2 * self.in_features + 16) <= 48 * 1024):
             y = self.gemv(x, bias=self.bias)
         else:
             y = prefill_linear(self, x)

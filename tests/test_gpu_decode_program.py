@@ -104,7 +104,11 @@ def test_program_attn_matches_kernel_and_oracle(K, H, G, hs, pos, max_seq, B, sp
     assert (y.cpu().float() - want).abs().max() <= 2 ** -7 * max(1.0, want.abs().max().item())
     assert torch.equal(z, K.qgemv_tiled(y, t, 64, d, "nf4", bs))
     if splits:  # same split count => same merge order => identical bits as the stand-alone kernel
-        y_k = K.attn_decode(qkv.cuda(), cos.cuda(), sin.cuda(), posd, kc.cuda(), vc.cuda(), H, G, hs, n_elem, num_splits=splits)
+        prev = K.attn_decode_tune(force_scalar=True)  # the program runs the scalar body for every shape
+        try:
+            y_k = K.attn_decode(qkv.cuda(), cos.cuda(), sin.cuda(), posd, kc.cuda(), vc.cuda(), H, G, hs, n_elem, num_splits=splits)
+        finally:
+            K.attn_decode_tune(force_scalar=prev)
         assert torch.equal(y, y_k)
 
 

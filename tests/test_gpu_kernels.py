@@ -297,6 +297,35 @@ def test_attn_decode(K, H, G, hs, pos, max_seq, B, splits, table_dtype):
     assert torch.equal(y, y2)
 
 
+@pytest.mark.parametrize("H,G,n_elem", [(64, 8, 128), (32, 4, 128), (16, 1, 128), (6, 2, 128), (8, 2, 32), (32, 16, 128)])
+@pytest.mark.parametrize("pos,max_seq,B,splits", [(0, 40, 1, 0), (31, 64, 2, 1), (32, 64, 1, 2), (700, 1024, 2, 0), (4095, 4096, 1, 0), (130, 300, 1, 64)])
+def test_attn_decode_gqa_mma_vs_oracle_and_scalar(K, H, G, n_elem, pos, max_seq, B, splits):
+    """Grouped-query decode attention on mma.sync (head size 128, q_per_kv 2..16) against the oracle formulation and against the
+    scalar kernel on the same inputs (same cache append bit for bit; outputs within the bf16 bar of test_attn_decode)."""
+    hs = 128
+    g = torch.Generator().manual_seed(H * 77 + pos)
+    qkv = torch.randn(B, (H + 2 * G) * hs, generator=g).bfloat16()
+    kc = torch.randn(B, G, max_seq, hs, generator=g).bfloat16()
+    vc = torch.randn(B, G, max_seq, hs, generator=g).bfloat16()
+    kc[:, :, pos:], vc[:, :, pos:] = 1e4, 1e4   # stale rows past the filled region must never be read
+    cos, sin = M.build_rope_cache(max_seq, n_elem, pos_dtype=torch.float32)
+    want, kc_ref, vc_ref = _attn_oracle(qkv, cos, sin, pos, kc, vc, H, G, hs, n_elem)
+    posd = torch.tensor([pos], device="cuda")
+    kcd, vcd = kc.cuda(), vc.cuda()
+    y = K.attn_decode(qkv.cuda(), cos.cuda(), sin.cuda(), posd, kcd, vcd, H, G, hs, n_elem, num_splits=splits)
+    assert torch.equal(kcd.cpu(), kc_ref) and torch.equal(vcd.cpu(), vc_ref), "cache append differs from the oracle"
+    tol = 2 ** -7 * max(1.0, want.abs().max().item())
+    assert (y.cpu().float() - want).abs().max() <= tol
+    prev = K.attn_decode_tune(force_scalar=True)
+    try:
+        kcs, vcs = kc.cuda(), vc.cuda()
+        ys = K.attn_decode(qkv.cuda(), cos.cuda(), sin.cuda(), posd, kcs, vcs, H, G, hs, n_elem, num_splits=splits)
+    finally:
+        K.attn_decode_tune(force_scalar=prev)
+    assert torch.equal(kcs, kcd) and torch.equal(vcs, vcd)
+    assert (y.float() - ys.float()).abs().max().item() <= tol
+
+
 def test_rope_kv_append(K):
     B, T, H, G, hs, max_seq = 2, 9, 8, 2, 128, 32
     g = torch.Generator().manual_seed(0)

@@ -1,7 +1,7 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k "prefill or rope_kv" > gpurun_out/pytest_prefill.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/pytest_prefill.log
-timeout 900 python -m pytest tests/test_gpu_model.py -m gpu -x -q > gpurun_out/pytest_model.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_model.log
-timeout 600 python tools/prefill_bench.py > gpurun_out/prefill_mistral.log 2>&1; tail -2 gpurun_out/prefill_mistral.log
-timeout 600 python tools/prefill_bench.py --model Llama-2-7b-hf --qt nf4 > gpurun_out/prefill_llama.log 2>&1; tail -2 gpurun_out/prefill_llama.log
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+for WL in mistral-7b-int4-bs1 llama2-7b-nf4-bs1; do
+timeout 600 python bench.py --no-cpu-baseline --steps 128 --workload $WL > gpurun_out/bench_$WL.json 2> gpurun_out/bench_$WL.err; echo "bench $WL rc=$?"; cut -c1-200 gpurun_out/bench_$WL.json
+done
