@@ -337,6 +337,9 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     return v;
   };
 
+  // int4 unpack constants kept in registers (opaque to constant propagation so that they stay register operands)
+  uint32_t i4mask = 0x000F000Fu, i4magic = 0x43004300u;
+  asm volatile("" : "+r"(i4mask), "+r"(i4magic));
   float acc0[NB][4], acc1[NB][4];
 #pragma unroll
   for (int nb = 0; nb < NB; ++nb) {
@@ -373,11 +376,19 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
         // one LOP3 yields the bf16 pair (128 + e_2p, 128 + e_2p+1); the +128 joins the zero-point term below
         const int sh = 8 * (j & 1);
         const uint32_t ua = (j < 2) ? w0.x : w0.y, ub = (j < 2) ? w0.z : w0.w, va = (j < 2) ? w1.x : w1.y, vb = (j < 2) ? w1.z : w1.w;
-        const uint32_t m = 0x000F000Fu, c = 0x43004300u;
+        // (w >> s) & 0x000F000F | 0x43004300 as ONE three-input LOP3 (mask and magic in registers: with two immediates
+        // the compiler emits two LOP3 per word)
+        auto ex = [&](uint32_t w, int s) -> uint32_t {
+          uint32_t r;
+          asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(s ? w >> s : w), "r"(i4mask), "r"(i4magic));
+          return r;
+        };
+        const uint32_t a0 = ex(ua, sh), a1 = ex(ub, sh), a2 = ex(ua, sh + 4), a3 = ex(ub, sh + 4);
+        const uint32_t b0 = ex(va, sh), b1 = ex(vb, sh), b2 = ex(va, sh + 4), b3 = ex(vb, sh + 4);
 #pragma unroll
         for (int nb = 0; nb < NB; ++nb) {
-          mma16816(p0[nb], ((ua >> sh) & m) | c, ((ub >> sh) & m) | c, ((ua >> (sh + 4)) & m) | c, ((ub >> (sh + 4)) & m) | c, xb[nb][2 * j], xb[nb][2 * j + 1]);
-          mma16816(p1[nb], ((va >> sh) & m) | c, ((vb >> sh) & m) | c, ((va >> (sh + 4)) & m) | c, ((vb >> (sh + 4)) & m) | c, xb[nb][2 * j], xb[nb][2 * j + 1]);
+          mma16816(p0[nb], a0, a1, a2, a3, xb[nb][2 * j], xb[nb][2 * j + 1]);
+          mma16816(p1[nb], b0, b1, b2, b3, xb[nb][2 * j], xb[nb][2 * j + 1]);
         }
         continue;
       }

@@ -1,7 +1,6 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
-for WL in mistral-7b-int4-bs1 llama2-7b-nf4-bs1; do
-timeout 600 python bench.py --no-cpu-baseline --steps 128 --workload $WL > gpurun_out/bench_$WL.json 2> gpurun_out/bench_$WL.err; echo "bench $WL rc=$?"; cut -c1-200 gpurun_out/bench_$WL.json
-done
+timeout 1200 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k "int4" > gpurun_out/pytest_int4.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_int4.log
+timeout 300 python tools/gemv_bench.py --qt int4 --l2pf 0 > gpurun_out/gemv_int4.log 2>&1; tail -1 gpurun_out/gemv_int4.log | cut -c1-200
+timeout 300 python tools/gemv_bench.py --qt int4 --l2pf 0 --model Llama-2-13b-hf --batch 4 > gpurun_out/gemv_int4_13b_b4.log 2>&1; tail -1 gpurun_out/gemv_int4_13b_b4.log | cut -c1-1500
