@@ -237,6 +237,16 @@ int b200_embedding(const void* idx, int idx_is_int64, const void* wte, void* out
 int b200_argmax(const void* logits, int64_t batch, int64_t vocab, int64_t stride, void* token_out,
                 int token_is_int64, void* pos_inout, int pos_is_int64, void* history, int64_t history_len,
                 b200_stream_t stream);
+/* stochastic sampling of batch row 0: sample() / multinomial_num_samples_1() of generate/base.py:22-41 as one launch.
+ * logits: vocab values (bf16 or fp32).  top_k <= 0 or >= vocab: no truncation, else only the top_k largest logits are
+ * kept (ties at the threshold in index order).  temperature > 0: token = argmax_i softmax(l / T)_i / e_i with
+ * e_i ~ Exp(1) (the draw the reference uses under torch.compile, base.py:23-26); temperature <= 0: argmax.
+ * rng_state: device int64[2] = {seed, offset}; e_i comes from Philox4x32-10(seed, offset, i) and offset is advanced
+ * by one per call (so a captured CUDA graph draws fresh numbers on every replay).  noise (optional, fp32[vocab]):
+ * use these Exp(1) values instead (tests).  token / pos / history bookkeeping exactly as b200_argmax. */
+int b200_sample(const void* logits, int logits_dtype, int64_t vocab, float temperature, int top_k, void* rng_state,
+                const void* noise, void* token_out, int token_is_int64, void* pos_inout, int pos_is_int64, void* history,
+                int64_t history_len, b200_stream_t stream);
 
 /* ---- persistent decode step: a whole T = 1 forward (embedding, every block, lm_head) as ONE kernel launch ------
  * Replaces the per-token call chain generate/base.py:44-47 -> lit_gpt/model.py:499-519 -> 572-593 (x n_layer).

@@ -131,6 +131,8 @@ _SIGNATURES = {
                                   c_float, c_void_p]),
     "b200_embedding": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p]),
     "b200_argmax": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int, c_void_p, c_int, c_void_p, c_int64, c_void_p]),
+    "b200_sample": (c_int, [c_void_p, c_int, c_int64, c_float, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_int64,
+                            c_void_p]),
     "b200_qgemm_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64]),
     "b200_qgemm": (c_int, [ctypes.POINTER(QGemmArgs), c_void_p]),
 }

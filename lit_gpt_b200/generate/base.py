@@ -31,7 +31,23 @@ def multinomial_num_samples_1(probs: torch.Tensor) -> torch.Tensor:
     return torch.multinomial(probs, num_samples=1)
 
 
+_RNG: Dict[torch.device, torch.Tensor] = {}
+
+
+def _rng_for(device: torch.device) -> torch.Tensor:
+    """Per-device Philox state of the fused sampler, (re)seeded from torch's seed so ``seed_everything`` is honoured."""
+    st = _RNG.get(device)
+    if st is None or int(st[0].item()) != torch.initial_seed():
+        st = _RNG[device] = K.new_rng_state(device)
+    return st
+
+
 def sample(logits: torch.Tensor, temperature: float = 1.0, top_k: Optional[int] = None) -> torch.Tensor:
+    if logits.is_cuda and logits.dtype in (torch.bfloat16, torch.float32) and logits.dim() == 3:
+        # one fused launch (csrc/sample.cu): top-k threshold, temperature softmax, the Exp(1) draw of base.py:23-26
+        out = torch.empty(1, dtype=torch.int64, device=logits.device)
+        K.sample_(logits, out, temperature, top_k, None if temperature <= 0.0 else _rng_for(logits.device))
+        return out
     logits = logits[0, -1]
     if top_k is not None:
         v, i = torch.topk(logits, min(top_k, logits.size(-1)))
@@ -59,17 +75,15 @@ class DecodeGraph:
         self.pos = torch.zeros(1, dtype=torch.int64, device=dev)
         self.history = torch.zeros(model.max_seq_length + 1, dtype=dtype, device=dev)
         self.max_seq_length = model.max_seq_length
+        self.rng = K.new_rng_state(dev)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
 
     def _step(self) -> None:
         logits = self.model(self.token.view(1, 1), self.pos)
         if self.temperature == 0.0 and self.top_k is None:
             K.argmax_(logits, self.token, pos_inout=self.pos, history=self.history)  # greedy: fused argmax + bookkeeping
-        else:
-            nxt = sample(logits, temperature=self.temperature, top_k=self.top_k).to(self.token.dtype)
-            self.token.copy_(nxt)
-            self.pos.add_(1)
-            self.history.index_copy_(0, self.pos, self.token)
+        else:  # stochastic: the fused sampler draws, advances its Philox offset and does the same bookkeeping
+            K.sample_(logits, self.token, self.temperature, self.top_k, self.rng, pos_inout=self.pos, history=self.history)
 
     def capture(self) -> None:
         state = (self.token.clone(), self.pos.clone())

@@ -336,6 +336,38 @@ def argmax_(logits: torch.Tensor, token_out: torch.Tensor, pos_inout: Optional[t
                                  C.stream_ptr(logits.device)), "argmax")
 
 
+def new_rng_state(device: torch.device, seed: Optional[int] = None) -> torch.Tensor:
+    """Device-side Philox state for ``sample_``: int64[2] = (seed, offset).  The seed defaults to torch's current seed, so
+    ``seed_everything`` (generate/base.py:140) makes the draws reproducible."""
+    return torch.tensor([torch.initial_seed() if seed is None else seed, 0], dtype=torch.int64, device=device)
+
+
+def sample_(logits: torch.Tensor, token_out: torch.Tensor, temperature: float = 1.0, top_k: Optional[int] = None,
+            rng_state: Optional[torch.Tensor] = None, pos_inout: Optional[torch.Tensor] = None, history: Optional[torch.Tensor] = None,
+            noise: Optional[torch.Tensor] = None) -> None:
+    """token_out[0] = one draw from softmax(top_k(logits[0, -1]) / temperature) (generate/base.py:22-41), on the device;
+    optionally pos_inout[0] += 1 and history[pos] = token like ``argmax_``.  ``noise``: Exp(1) values to use instead of Philox."""
+    C.require_cuda(logits, token_out)
+    if logits.dtype not in (torch.bfloat16, torch.float32):
+        raise C.B200Error(f"sample_: logits must be bf16 or fp32 (got {logits.dtype})")
+    V = logits.shape[-1]
+    row = (logits[0, -1] if logits.dim() == 3 else logits[0] if logits.dim() == 2 else logits).contiguous()  # base.py:31
+    if history is not None and history.dtype != token_out.dtype:
+        raise C.B200Error("sample_: history must have the dtype of token_out")
+    if temperature > 0.0 and rng_state is None and noise is None:
+        raise C.B200Error("sample_: temperature > 0 needs rng_state (K.new_rng_state) or noise")
+    if rng_state is not None and (rng_state.dtype != torch.int64 or rng_state.numel() != 2 or not rng_state.is_cuda):
+        raise C.B200Error("sample_: rng_state must be a CUDA int64[2] tensor")
+    if noise is not None:
+        noise = noise.to(torch.float32).contiguous()
+        if noise.numel() != V:
+            raise C.B200Error("sample_: noise must hold one value per vocabulary entry")
+    C.check(C.load().b200_sample(row.data_ptr(), C.DTYPE_CODE[row.dtype], V, float(temperature), int(top_k or 0), C.ptr(rng_state), C.ptr(noise),
+                                 token_out.data_ptr(), int(token_out.dtype == torch.int64), C.ptr(pos_inout),
+                                 int(pos_inout is not None and pos_inout.dtype == torch.int64), C.ptr(history),
+                                 0 if history is None else history.numel(), C.stream_ptr(logits.device)), "sample")
+
+
 # ---------------------------------------------------------------------------------------------------------
 # attention
 # ---------------------------------------------------------------------------------------------------------

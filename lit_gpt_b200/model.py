@@ -85,7 +85,8 @@ class GPT(nn.Module):
         if input_pos is not None:
             if self.mask_cache is None:
                 raise TypeError("You need to call `gpt.set_kv_cache()`")
-            if T == 1 and input_pos.numel() == 1 and self.fused_decode_ready(idx):
+            # (a traced forward takes the module path: its kernels are registered custom ops, the fused chain is raw C-ABI calls)
+            if T == 1 and input_pos.numel() == 1 and not torch.compiler.is_compiling() and self.fused_decode_ready(idx):
                 return self._fused_decode(idx, input_pos)
             cos = self.cos.index_select(0, input_pos)
             sin = self.sin.index_select(0, input_pos)
@@ -427,6 +428,15 @@ class CausalSelfAttention(nn.Module):
                                 mask: Optional[torch.Tensor], input_pos: torch.Tensor) -> torch.Tensor:
         c, cache = self.config, self.kv_cache
         B, T, _ = qkv.shape
+        if torch.compiler.is_compiling():  # traced: opaque b200gpt::* nodes with declared cache mutation (ops.py), no graph break
+            from . import ops  # noqa: F401
+
+            o = torch.ops.b200gpt
+            if T == 1:
+                y = o.attn_decode(qkv, cos, sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups, c.head_size, c.rope_n_elem, True)
+                return y.view(B, 1, c.n_head * c.head_size)
+            q = o.rope_kv_append(qkv, cos, sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups, c.head_size, c.rope_n_elem, True)
+            return o.attn_prefill(q, cache.k, cache.v, input_pos, 1.0 / math.sqrt(c.head_size))
         if T == 1:
             y = K.attn_decode(qkv, cos, sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups, c.head_size,
                               c.rope_n_elem, table_preselected=True)
@@ -487,7 +497,7 @@ class LLaMAMLP(nn.Module):
         rows = x.numel() // x.size(-1)
         if (isinstance(f1, QLinear) and isinstance(f2, QLinear) and f1.is_quantized and f2.is_quantized and x.is_cuda
                 and x.dtype == torch.bfloat16 and rows <= 16 and f1.bias is None and f2.bias is None
-                and f1.quant_type == f2.quant_type and f1.quant_type != "int8"):
+                and f1.quant_type == f2.quant_type and f1.quant_type != "int8" and not torch.compiler.is_compiling()):
             # gate and up projections + SwiGLU in one pass over both weight matrices
             return self.proj(f1.gemv(x, other=f2))
         x_fc_1 = self.fc_1(x)

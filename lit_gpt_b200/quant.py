@@ -203,6 +203,15 @@ class QLinear(nn.Module):
         if in_dtype != torch.bfloat16:
             x = x.to(torch.bfloat16)
         rows = x.numel() // self.in_features
+        if torch.compiler.is_compiling():  # traced: one opaque b200gpt::qlinear* node (lit_gpt_b200/ops.py), no graph break
+            from . import ops  # noqa: F401
+
+            if self.tiled is not None and rows * (2 * self.in_features + 16) <= 48 * 1024 and rows <= GEMV_MAX_ROWS:
+                y = torch.ops.b200gpt.qlinear_tiled(x, self.tiled, self.out_features, self.in_features, self.quant_type, self.blocksize, self.bias)
+            else:
+                y = torch.ops.b200gpt.qlinear(x, self.weight.data, self.scale, self.out_features, self.in_features, self.quant_type,
+                                              self.blocksize, self.bias)
+            return y if in_dtype == torch.bfloat16 else y.to(in_dtype)
         # <= 16 rows: the streaming GEMV, provided the activation rows fit its shared-memory plan (a 16-token prompt at
         # K = 8192 does not: that call is a small prefill and takes the GEMM); shapes without a tiled layout (toy
         # configs) keep the reference-layout GEMV

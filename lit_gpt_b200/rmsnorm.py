@@ -21,6 +21,10 @@ class RMSNorm(torch.nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16 and self.dim in (-1, x.dim() - 1):
+            if torch.compiler.is_compiling():  # traced: one opaque b200gpt::rmsnorm node (lit_gpt_b200/ops.py), no graph break
+                from . import ops  # noqa: F401
+
+                return torch.ops.b200gpt.rmsnorm(x, self.weight, self.eps)
             return K.rmsnorm(x, self.weight, self.eps)
         dtype = x.dtype
         x = x.float()

@@ -197,3 +197,23 @@ def test_tp2_matches_single_gpu(tmp_path):
            "--master-port", "29631", os.path.join(root, "tests", "tp_gpu_worker.py"), root]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "TP_GPU_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+
+
+@torch.inference_mode(False)
+def test_traced_forward_has_no_graph_breaks():
+    """Mirror of the reference's tests/test_model.py:564-575: dynamo traces GPT.forward (prefill and the cached decode call)
+    without graph breaks, because every kernel is a registered b200gpt::* custom op with a fake kernel (lit_gpt_b200/ops.py)."""
+    import torch._dynamo
+
+    from lit_gpt_b200 import Config
+
+    kw = dict(name="trace", block_size=64, vocab_size=512, padded_vocab_size=512, n_layer=2, n_head=4, n_query_groups=2, n_embd=256,
+              rotary_percentage=1.0, parallel_residual=False, bias=False, _norm_class="RMSNorm", _mlp_class="LLaMAMLP", intermediate_size=512)
+    p = M.init_weights(M.RefConfig.from_any(Config(**kw)), seed=3, dtype=torch.bfloat16)
+    model = build_cuda_model(kw, p, "nf4", max_seq=32)
+    x = torch.tensor([[3, 1, 4, 1, 5]], device="cuda")
+    with torch.no_grad():
+        for inp, pos in ((x, torch.arange(5, device="cuda")), (x[:, :1], torch.tensor([5], device="cuda"))):
+            torch._dynamo.reset()
+            ex = torch._dynamo.explain(model)(inp, pos)
+            assert ex.graph_break_count == 0 and ex.graph_count == 1, (ex.break_reasons, ex.graph_count)
