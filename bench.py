@@ -29,6 +29,9 @@ WORKLOADS = {
     "llama2-7b-nf4-bs1": ("Llama-2-7b-hf", "nf4", 1, 16, 0),
     "llama2-7b-nf4-bs1-ctx2048": ("Llama-2-7b-hf", "nf4", 1, 16, 2032),
     "llama2-13b-int4-bs1-ctx2048": ("Llama-2-13b-hf", "int4", 1, 16, 2032),
+    "llama2-13b-int4-bs4-ctx2048": ("Llama-2-13b-hf", "int4", 4, 16, 2032),
+    "llama2-13b-int4-bs16-ctx2048": ("Llama-2-13b-hf", "int4", 16, 16, 2032),
+    "mistral-7b-int4-bs1-ctx3936": ("Mistral-7B-v0.1", "int4", 1, 16, 3920),  # block_size 4096 bounds prompt + steps
     "mistral-7b-int4-bs1": ("Mistral-7B-v0.1", "int4", 1, 16, 0),
     "llama2-70b-int4-bs1-ctx2048": ("Llama-2-70b-hf", "int4", 1, 16, 2032),
 }

@@ -95,8 +95,6 @@ __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<H
   const int h0 = hc * QPK;                                     // first query head (within the group) of this item
   const int nh = min(QPK, p.qpk - h0);                         // live heads
 
-  int64_t pos = p.pos_i64 ? *reinterpret_cast<const int64_t*>(p.pos) : (int64_t)*reinterpret_cast<const int32_t*>(p.pos);
-  pos = pos < 0 ? 0 : (pos >= p.max_seq ? p.max_seq - 1 : pos);  // host validates; never index out of bounds
   const bool last_split = split == p.nsplit - 1;
 
   // ---- q (and, in the last split, the new k / v): load, RoPE, keep as bf16-exact floats in smem -----------
@@ -106,11 +104,16 @@ __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<H
   const __nv_bfloat16* grp = p.qkv + ((int64_t)b * p.n_groups + gi) * (p.qpk + 2) * HS;
   float (&raw_q)[QPK][HS] = s_acc[0];
   float* raw_k = s_acc[1][0];
+  float rq[QPK], rk = 0.f, rv = 0.f;
   if (tid < HS) {
-    float rq[QPK], rk = 0.f, rv = 0.f;
 #pragma unroll
     for (int h = 0; h < QPK; ++h) rq[h] = h < nh ? ld_act_bf16(grp + (h0 + h) * HS + tid) : 0.f;
     if (last_split) { rk = ld_act_bf16(grp + p.qpk * HS + tid); rv = ld_act_bf16(grp + (p.qpk + 1) * HS + tid); }
+  }
+  // the position is loaded AFTER the activation loads were issued (they do not depend on it): one round trip, not two
+  int64_t pos = p.pos_i64 ? __ldcg(reinterpret_cast<const long long*>(p.pos)) : (int64_t)__ldcg(reinterpret_cast<const int*>(p.pos));
+  pos = pos < 0 ? 0 : (pos >= p.max_seq ? p.max_seq - 1 : pos);  // host validates; never index out of bounds
+  if (tid < HS) {
 #pragma unroll
     for (int h = 0; h < QPK; ++h) raw_q[h][tid] = rq[h];
     raw_k[tid] = rk;

@@ -98,8 +98,10 @@ int b200_attn_decode(const b200_attn_decode_args* a, b200_stream_t stream) {
   int nsplit = a->num_splits;
   if (nsplit <= 0) {
     const int ctas = a->batch * a->n_groups * head_chunks;
-    nsplit = ((gqa ? 1 : 2) * sm_count() + ctas - 1) / ctas;
-    const int by_len = gqa ? (a->max_seq + 255) / 256 : (a->max_seq + 63) / 64;   // two 32-key tiles per warp at least
+    // measured (tools/attn_bench.py --splits): the kernels are bound by dependent round trips, so short key ranges per
+    // CTA win until the merge grows; about 3 CTAs per SM for the scalar kernel, 1 for the tensor-core one
+    nsplit = ((gqa ? 1 : 3) * sm_count() + ctas - 1) / ctas;
+    const int by_len = gqa ? (a->max_seq + 255) / 256 : (a->max_seq + 31) / 32;   // gqa: two 32-key tiles per warp at least
     if (nsplit > by_len) nsplit = by_len;
   }
   if (nsplit > 64) nsplit = 64;

@@ -37,7 +37,7 @@ _RNG: Dict[torch.device, torch.Tensor] = {}
 def _rng_for(device: torch.device) -> torch.Tensor:
     """Per-device Philox state of the fused sampler, (re)seeded from torch's seed so ``seed_everything`` is honoured."""
     st = _RNG.get(device)
-    if st is None or int(st[0].item()) != torch.initial_seed():
+    if st is None or int(st[0].item()) != (torch.initial_seed() & 0x7FFFFFFFFFFFFFFF):
         st = _RNG[device] = K.new_rng_state(device)
     return st
 

@@ -339,7 +339,8 @@ def argmax_(logits: torch.Tensor, token_out: torch.Tensor, pos_inout: Optional[t
 def new_rng_state(device: torch.device, seed: Optional[int] = None) -> torch.Tensor:
     """Device-side Philox state for ``sample_``: int64[2] = (seed, offset).  The seed defaults to torch's current seed, so
     ``seed_everything`` (generate/base.py:140) makes the draws reproducible."""
-    return torch.tensor([torch.initial_seed() if seed is None else seed, 0], dtype=torch.int64, device=device)
+    seed = (torch.initial_seed() if seed is None else int(seed)) & 0x7FFFFFFFFFFFFFFF  # torch's default seed is a full uint64
+    return torch.tensor([seed, 0], dtype=torch.int64, device=device)
 
 
 def sample_(logits: torch.Tensor, token_out: torch.Tensor, temperature: float = 1.0, top_k: Optional[int] = None,
