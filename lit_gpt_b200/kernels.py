@@ -102,6 +102,27 @@ def double_quant_absmax(absmax: torch.Tensor, offset: Optional[float] = None):
     return q, a2, offset, deq
 
 
+def dequant_absmax(qabs: torch.Tensor, absmax2: torch.Tensor, offset: float) -> torch.Tensor:
+    """Load-time inverse of ``double_quant_absmax`` for pre-quantized checkpoints: fp32 absmax = code[q] * absmax2[i // 256]
+    + offset with the kernel's two separate roundings (csrc/quantize.cu), so a reloaded module streams identical statistics."""
+    C.require_cuda(qabs, absmax2)
+    code = dynamic_map(qabs.device)
+    n = qabs.numel()
+    m = absmax2.float().repeat_interleave(256)[:n]
+    return (code[qabs.long()] * m + torch.tensor(float(offset), dtype=torch.float32, device=qabs.device)).contiguous()
+
+
+def int4_fuse_scale_zero(scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
+    """Load-time rebuild of the kernel-side ``sz`` tensor, int32 (N, G) = half2{scale, zero} (low half: fp16 scale bits, high
+    half: the 4-bit zero-point as fp16), from the checkpoint tensors of ``quantize_int4``.  Bit-exact to the quantizer's own."""
+    N, G = scales.shape
+    shifts = torch.arange(0, 32, 4, device=qzeros.device, dtype=torch.int32)
+    z = ((qzeros.to(torch.int32).unsqueeze(-1) >> shifts) & 0xF).reshape(N, -1)[:, :G]
+    lo = scales.contiguous().view(torch.int16).to(torch.int32) & 0xFFFF
+    hi = z.to(torch.float16).view(torch.int16).to(torch.int32) & 0xFFFF
+    return (lo | (hi << 16)).contiguous()
+
+
 # ---------------------------------------------------------------------------------------------------------
 # bnb.int8 (LLM.int8())
 # ---------------------------------------------------------------------------------------------------------

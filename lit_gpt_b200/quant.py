@@ -124,6 +124,59 @@ class QLinear(nn.Module):
         if K.tiled_bytes(shape[0], shape[1], self.quant_type):
             self.tiled = K.tile_4bit(self.weight.data, self.scale, shape[0], shape[1], self.quant_type, self.blocksize)
 
+    # -- pre-quantized checkpoints: the packed tensors go to disk as they are, no re-quantisation on load --
+    def export_packed(self) -> dict:
+        """CPU copies of exactly what ``quantize_`` produced (packed codes + statistics), keyed for ``import_packed``."""
+        if not self.is_quantized:
+            raise B200Error("export_packed: the module is not quantized yet")
+        out = {"mode": self.mode, "shape": tuple(self.quant_state[1]), "weight": self.weight.data.cpu()}
+        if self.quant_type == "int8":
+            out["SCB"] = self.SCB.cpu()
+        elif self.quant_type == "int4":
+            out["scales"], out["qzeros"] = self.scales.cpu(), self.qzeros.cpu()
+        elif self.double_quant:
+            qs = self.quant_state
+            out["qabsmax"], out["offset"], out["absmax2"] = qs[0].cpu(), qs[4][0].cpu() if torch.is_tensor(qs[4][0]) else qs[4][0], qs[4][1][0].cpu()
+        else:
+            out["absmax"] = self.absmax.cpu()
+        if self.bias is not None:
+            out["bias"] = self.bias.data.cpu()
+        return out
+
+    @torch.no_grad()
+    def import_packed(self, st: dict, device: torch.device) -> None:
+        """Inverse of ``export_packed`` on ``device``: installs the packed tensors, rebuilds ``quant_state`` and the tiled
+        kernel layout (a byte permutation, csrc/tile.cu).  The weights are NOT re-quantized."""
+        if st["mode"] != self.mode:
+            raise B200Error(f"checkpoint mode {st['mode']!r} does not match module mode {self.mode!r}")
+        shape = tuple(st["shape"])
+        if shape != (self.out_features, self.in_features):
+            raise B200Error(f"packed shape {shape} does not match ({self.out_features}, {self.in_features})")
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise B200Error("import_packed: quantized modules live on CUDA only")
+        self.weight = nn.Parameter(st["weight"].to(dev), requires_grad=False)
+        self.scales = self.qzeros = self.sz = self.tiled = self.absmax = self.SCB = None
+        if self.quant_type == "int8":
+            self.SCB = st["SCB"].to(dev)
+            self.quant_state = [self.SCB, torch.Size(shape), torch.float16, None, None, "int8", None]
+        elif self.quant_type == "int4":
+            self.scales, self.qzeros = st["scales"].to(dev), st["qzeros"].to(dev)
+            self.sz = K.int4_fuse_scale_zero(self.scales, self.qzeros)
+            self.quant_state = [self.scales, torch.Size(shape), self.compute_dtype, self.blocksize, None, "int4", None]
+        elif self.double_quant:
+            qabs, absmax2 = st["qabsmax"].to(dev), st["absmax2"].to(dev)
+            offset = st["offset"].to(dev) if torch.is_tensor(st["offset"]) else st["offset"]
+            self.absmax = K.dequant_absmax(qabs, absmax2, offset)
+            self.quant_state = [qabs, torch.Size(shape), self.compute_dtype, self.blocksize, [offset, [absmax2, K.dynamic_map(dev), 256]], self.quant_type, None]
+        else:
+            self.absmax = st["absmax"].to(dev)
+            self.quant_state = [self.absmax, torch.Size(shape), self.compute_dtype, self.blocksize, None, self.quant_type, None]
+        if "bias" in st and self.bias is not None:
+            self.bias = nn.Parameter(st["bias"].to(dev), requires_grad=False)
+        if self.quant_type != "int8" and K.tiled_bytes(shape[0], shape[1], self.quant_type):
+            self.tiled = K.tile_4bit(self.weight.data, self.scale, shape[0], shape[1], self.quant_type, self.blocksize)
+
     def dequantize(self, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
         """(out_features, in_features) tensor of code[c] * absmax — bit-exact to oracle/quant_ref.py."""
         if not self.is_quantized:
