@@ -202,7 +202,10 @@ class GPT(nn.Module):
         from .p2p import PeerComm
 
         blocks = list(self.transformer.h)
-        lins = [self.lm_head] + [l for b in blocks for l in (b.attn.attn, b.attn.proj, b.mlp.fc_1, b.mlp.fc_2, b.mlp.proj)]
+        # mlp.proj may lack a tiled layout (row-parallel shard whose in_features is not a multiple of the quantisation block,
+        # e.g. 11008 / 8): that hand-off alone then stays an NCCL all-reduce, the attention branch still uses peer memory
+        lins = [self.lm_head] + [l for b in blocks for l in (b.attn.attn, b.attn.proj, b.mlp.fc_1, b.mlp.fc_2)]
+        lins += [b.mlp.proj for b in blocks if b.mlp.proj.tiled is not None]
         ok = (os.environ.get("B200_TP_NCCL", "0") != "1" and all(l.tiled is not None for l in lins)
               and all(16 * (2 * l.in_features + 16) <= 48 * 1024 or batch * (2 * l.in_features + 16) <= 48 * 1024 for l in lins))
         comm: Any = False
@@ -306,13 +309,19 @@ class GPT(nn.Module):
                 return K.qgemv_tiled(inp, q.tiled, q.out_features, q.in_features, q.quant_type, q.blocksize,
                                      tiled2=None if other is None else other.tiled, tp=comm.handoff(send, recv), **kw)
 
+            # pending: how the previous block's MLP output reaches the next prologue: "p2p" (slots of buffer 1), a tensor
+            # (NCCL all-reduced delta; the collective also orders the ranks, so reusing buffer 0 next block stays race-free)
+            pending: Any = None
             for li, block in enumerate(blocks):
                 a, m, cache = block.attn, block.mlp, block.attn.kv_cache
-                if li == 0:
+                if pending is None:
                     qkv = lin(a.attn, x, norm_weight=block.norm_1.weight, norm_eps=eps)
                 else:
                     x_new = torch.empty_like(x)
-                    qkv = tlin(a.attn, x, recv=1, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps)
+                    if isinstance(pending, str):
+                        qkv = tlin(a.attn, x, recv=1, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps)
+                    else:
+                        qkv = lin(a.attn, x, delta=pending, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps)
                     x = x_new
                 y = K.attn_decode(qkv, self.cos, self.sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups,
                                   c.head_size, c.rope_n_elem)
@@ -320,11 +329,15 @@ class GPT(nn.Module):
                 x_new = torch.empty_like(x)
                 act = tlin(m.fc_1, x, other=m.fc_2, recv=0, x_out=x_new, norm_weight=block.norm_2.weight, norm_eps=eps)
                 x = x_new
-                tlin(m.proj, act, send=1)
-            if blocks:
+                if m.proj.tiled is not None:
+                    tlin(m.proj, act, send=1)
+                    pending = "p2p"
+                else:
+                    pending = self._all_reduce(lin(m.proj, act))
+            if isinstance(pending, str):
                 logits = tlin(self.lm_head, x, recv=1, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
             else:
-                logits = lin(self.lm_head, x, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+                logits = lin(self.lm_head, x, delta=pending, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
             return logits.view(B, 1, -1)
         for li, block in enumerate(blocks):
             a, m, cache = block.attn, block.mlp, block.attn.kv_cache
