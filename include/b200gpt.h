@@ -206,8 +206,9 @@ typedef struct b200_attn_decode_args {
 } b200_attn_decode_args;
 size_t b200_attn_decode_workspace_bytes(int batch, int n_head, int head_size, int max_splits);
 int b200_attn_decode(const b200_attn_decode_args* args, b200_stream_t stream);
-/* development / test knob: 1 = always use the scalar kernel (multi-head formulation) even for grouped-query shapes that
- * the mma.sync kernel covers (head_size 128, 2 <= q_per_kv <= 16).  Returns the previous setting. */
+/* development / test knob: 1 = always use the scalar kernel with the workspace merge, even for grouped-query shapes that
+ * the mma.sync kernel covers (head_size 128, 2 <= q_per_kv <= 16) and for split counts <= 8 that would otherwise run as a
+ * thread-block cluster merging through distributed shared memory.  Returns the previous setting. */
 int b200_attn_decode_tune(int force_scalar);
 
 /* ---- prefill helper: RoPE + KV-cache write for T > 1 tokens at positions pos[0..T) (lit_gpt/model.py:624-649).

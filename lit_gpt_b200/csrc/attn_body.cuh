@@ -68,6 +68,7 @@ struct AttnSmem {
   float k[HS], v[HS], tmp[HS];
   float acc[4][QPK][HS];
   float m[4][QPK], l[4][QPK];
+  float pm[QPK], pl[QPK];   // this CTA's split partial (m, l) when the splits merge through distributed shared memory
   unsigned int last;
 };
 
@@ -77,7 +78,10 @@ __device__ __forceinline__ float ld_act_bf16(const __nv_bfloat16* p) {
 }
 
 // tid in [0, 128); `sync()` is a barrier over exactly those 128 threads; `by` = group * head_chunks + head chunk
-template <int HS, int QPK, int DPL, typename Sync>
+// CLUSTER: the nsplit CTAs of one (batch, group, head chunk) form a thread-block cluster (launch attribute); their split
+// partials stay in shared memory and cluster rank 0 merges them through distributed shared memory -- no workspace, no
+// fence, no ticket, three dependent L2 round trips fewer than the workspace protocol.
+template <int HS, int QPK, int DPL, typename Sync, bool CLUSTER = false>
 __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<HS, QPK>& sm, const int tid, const int split, const int by,
                                                  const int b, Sync sync) {
   constexpr int LPK = HS / DPL, GPW = 32 / LPK, SLOTS = 4 * GPW, NR = DPL / 2;
@@ -255,15 +259,57 @@ __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<H
 #pragma unroll
       for (int w = 0; w < 4; ++w) a += s_acc[w][h][d] * c[w];
       if (p.nsplit == 1) p.out[((int64_t)b * H + head) * HS + d] = __float2bfloat16_rn(a / lt);
+      else if (CLUSTER) s_q[h][d] = a;   // q lives in registers by now: its shared-memory rows carry the split partial
       else __stcg(p.ws_acc + (((int64_t)b * H + head) * p.nsplit + split) * HS + d, a);
     }
     if (p.nsplit > 1 && tid == 0) {
-      float* ml = p.ws_ml + (((int64_t)b * H + head) * p.nsplit + split) * 2;
-      __stcg(ml, mn);
-      __stcg(ml + 1, lt);
+      if (CLUSTER) { sm.pm[h] = mn; sm.pl[h] = lt; }
+      else {
+        float* ml = p.ws_ml + (((int64_t)b * H + head) * p.nsplit + split) * 2;
+        __stcg(ml, mn);
+        __stcg(ml + 1, lt);
+      }
     }
   }
   if (p.nsplit == 1) return;
+  if constexpr (CLUSTER) {
+    // cluster barrier #1: every split's partial is in its CTA's shared memory
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (split == 0) {
+      const int NS = p.nsplit;
+      const uint32_t q_a = (uint32_t)__cvta_generic_to_shared(&s_q[0][0]);
+      const uint32_t pm_a = (uint32_t)__cvta_generic_to_shared(&sm.pm[0]), pl_a = (uint32_t)__cvta_generic_to_shared(&sm.pl[0]);
+      auto remote = [](uint32_t addr, int rank) -> float {
+        uint32_t ra;
+        float v;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(addr), "r"(rank));
+        asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+        return v;
+      };
+      for (int i = tid; i < nh * HS; i += 128) {
+        const int h = i / HS, d = i % HS;
+        float ms[8], ls[8], vs[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+          ms[r] = r < NS ? remote(pm_a + h * 4, r) : -INFINITY;
+          ls[r] = r < NS ? remote(pl_a + h * 4, r) : 0.f;
+          vs[r] = r < NS ? remote(q_a + (h * HS + d) * 4, r) : 0.f;
+        }
+        float mn = -INFINITY, lt = 0.f, a = 0.f;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) mn = fmaxf(mn, ms[r]);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) lt += ms[r] == -INFINITY ? 0.f : ls[r] * exp2f(ms[r] - mn);
+        const float inv = 1.f / lt;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) a = fmaf(vs[r], ms[r] == -INFINITY ? 0.f : exp2f(ms[r] - mn) * inv, a);
+        p.out[((int64_t)b * H + gi * p.qpk + h0 + h) * HS + d] = __float2bfloat16_rn(a);
+      }
+    }
+    // cluster barrier #2: no CTA leaves (and frees its shared memory) before rank 0 has read it
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    return;
+  }
 
   // ---- last CTA of this (batch, group, head chunk) merges the splits ---------------------------------------
   __threadfence();

@@ -23,6 +23,49 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
   attn_decode_item<HS, QPK, DPL>(p, sm, (int)threadIdx.x, (int)blockIdx.x, (int)blockIdx.y, (int)blockIdx.z, [] { __syncthreads(); });
 }
 
+struct CtaSync {
+  __device__ __forceinline__ void operator()() const { __syncthreads(); }
+};
+
+// same body; the nsplit (<= 8) CTAs along x are one thread-block cluster and merge through distributed shared memory
+template <int HS, int QPK, int DPL>
+__global__ void __launch_bounds__(128) attn_decode_cluster_kernel(const AttnParams p) {
+  __shared__ AttnSmem<HS, QPK> sm;
+  griddep_launch();
+  griddep_wait();
+  attn_decode_item<HS, QPK, DPL, CtaSync, true>(p, sm, (int)threadIdx.x, (int)blockIdx.x, (int)blockIdx.y, (int)blockIdx.z, CtaSync{});
+}
+
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_cluster(void (*kernel)(KArgs...), dim3 grid, dim3 block, unsigned cluster_x, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cluster_x;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_pdl.load(std::memory_order_relaxed) ? 2 : 1;
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
+template <int HS>
+static cudaError_t launch_attn_cluster(const AttnParams& p, int qpk_t, dim3 grid, cudaStream_t st) {
+  switch (qpk_t) {
+    case 1: return launch_cluster(attn_decode_cluster_kernel<HS, 1, 16>, grid, dim3(128), grid.x, st, p);
+    case 2: return launch_cluster(attn_decode_cluster_kernel<HS, 2, 16>, grid, dim3(128), grid.x, st, p);
+    case 4: return launch_cluster(attn_decode_cluster_kernel<HS, 4, 8>, grid, dim3(128), grid.x, st, p);
+    default: return launch_cluster(attn_decode_cluster_kernel<HS, 8, 4>, grid, dim3(128), grid.x, st, p);
+  }
+}
+
 // ---- prefill helper: RoPE + cache write for T > 1 (lit_gpt/model.py:624-649) --------------------------------
 // grid (T, n_groups, batch); q_out is (batch, n_head, T, hs) so torch SDPA / the prefill attention can consume it.
 template <typename PosT>
@@ -93,7 +136,8 @@ int b200_attn_decode(const b200_attn_decode_args* a, b200_stream_t stream) {
   const int qpk = a->n_head / a->n_groups;
   const int qpk_t = qpk == 1 ? 1 : (qpk == 2 ? 2 : (qpk <= 4 ? 4 : 8));
   // grouped / multi-query attention at head size 128: the heads of a group are the M rows of a tensor-core tile
-  const bool gqa = attn_decode_gqa_supported(a->head_size, qpk) && !g_attn_force_scalar.load(std::memory_order_relaxed);
+  const bool force_scalar = g_attn_force_scalar.load(std::memory_order_relaxed) != 0;
+  const bool gqa = attn_decode_gqa_supported(a->head_size, qpk) && !force_scalar;
   const int head_chunks = gqa ? 1 : (qpk + qpk_t - 1) / qpk_t;
   int nsplit = a->num_splits;
   if (nsplit <= 0) {
@@ -103,7 +147,11 @@ int b200_attn_decode(const b200_attn_decode_args* a, b200_stream_t stream) {
     nsplit = ((gqa ? 1 : 3) * sm_count() + ctas - 1) / ctas;
     const int by_len = gqa ? (a->max_seq + 255) / 256 : (a->max_seq + 31) / 32;   // gqa: two 32-key tiles per warp at least
     if (nsplit > by_len) nsplit = by_len;
+    // scalar kernel: cap at the portable cluster size so that the splits merge through distributed shared memory (the
+    // tensor-core kernel measured the same with 9..16 workspace-merged splits as with 8 clustered ones: not capped)
+    if (!gqa && !force_scalar && nsplit > 8) nsplit = 8;
   }
+  const bool cluster = !gqa && !force_scalar && nsplit >= 2 && nsplit <= 8;
   if (nsplit > 64) nsplit = 64;
   if (nsplit < 1) nsplit = 1;
   size_t need = b200_attn_decode_workspace_bytes(a->batch, a->n_head, a->head_size, nsplit);
@@ -128,6 +176,7 @@ int b200_attn_decode(const b200_attn_decode_args* a, b200_stream_t stream) {
   p.scale_log2 = (1.0f / sqrtf((float)a->head_size)) * 1.4426950408889634f;
   dim3 grid(nsplit, a->n_groups * head_chunks, a->batch);
   cudaError_t e = gqa ? launch_attn_decode_gqa(p, grid, (cudaStream_t)stream)
+                  : cluster ? (a->head_size == 128 ? launch_attn_cluster<128>(p, qpk_t, grid, (cudaStream_t)stream) : launch_attn_cluster<64>(p, qpk_t, grid, (cudaStream_t)stream))
                       : (a->head_size == 128 ? launch_attn<128>(p, qpk_t, grid, (cudaStream_t)stream) : launch_attn<64>(p, qpk_t, grid, (cudaStream_t)stream));
   if (e != cudaSuccess) {
     set_error("b200_attn_decode: launch failed: %s", cudaGetErrorString(e));

@@ -27,10 +27,14 @@ constexpr int kGqWarpBytes = 2 * kGqStage;                // two stages per warp
 constexpr int kGqQBytes = kGqRows * kGqHS * 2;
 constexpr int kGqSmem = 4 * kGqWarpBytes + kGqQBytes + 2 * kGqHS * 2;
 
+// CLUSTER: the nsplit (<= 8) CTAs of a (batch, group) are one thread-block cluster; split partials stay in shared memory
+// and cluster rank 0 merges them through distributed shared memory (no workspace, fence or ticket).
+template <bool CLUSTER>
 __global__ void __launch_bounds__(128, 1) attn_decode_gqa_kernel(const AttnParams p) {
   extern __shared__ __align__(128) uint8_t gq_smem[];
   constexpr int HS = kGqHS;
   __shared__ float s_m[4][kGqRows], s_l[4][kGqRows];
+  __shared__ float s_pm[kGqRows], s_pl[kGqRows];
   __shared__ unsigned int s_last;
   uint8_t* const sQ = gq_smem + 4 * kGqWarpBytes;                          // [16][HS] bf16, swizzled
   __nv_bfloat16* const s_nk = reinterpret_cast<__nv_bfloat16*>(sQ + kGqQBytes);  // new k row (roped), new v row
@@ -217,15 +221,55 @@ __global__ void __launch_bounds__(128, 1) attn_decode_gqa_kernel(const AttnParam
 #pragma unroll
       for (int w = 0; w < 4; ++w) a += c[w] == 0.f ? 0.f : warp_acc(w)[h * HS + d] * c[w];   // idle warps hold stale bytes
       if (p.nsplit == 1) p.out[((int64_t)b * H + head) * HS + d] = __float2bfloat16_rn(a / lt);
+      else if (CLUSTER) reinterpret_cast<float*>(gq_smem)[h * HS + d] = a;   // element (h, d) of warp 0's region: only this thread read it
       else __stcg(p.ws_acc + (((int64_t)b * H + head) * p.nsplit + split) * HS + d, a);
     }
     if (p.nsplit > 1 && tid == 0) {
-      float* ml = p.ws_ml + (((int64_t)b * H + head) * p.nsplit + split) * 2;
-      __stcg(ml, mn);
-      __stcg(ml + 1, lt);
+      if (CLUSTER) { s_pm[h] = mn; s_pl[h] = lt; }
+      else {
+        float* ml = p.ws_ml + (((int64_t)b * H + head) * p.nsplit + split) * 2;
+        __stcg(ml, mn);
+        __stcg(ml + 1, lt);
+      }
     }
   }
   if (p.nsplit == 1) return;
+  if constexpr (CLUSTER) {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (split == 0) {
+      const int NS = p.nsplit;
+      const uint32_t part_a = pf_smem(gq_smem), pm_a = pf_smem(&s_pm[0]), pl_a = pf_smem(&s_pl[0]);
+      auto remote = [](uint32_t addr, int rank) -> float {
+        uint32_t ra;
+        float v;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(addr), "r"(rank));
+        asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+        return v;
+      };
+      for (int i = tid; i < nh * HS; i += 128) {
+        const int h = i / HS;
+        float ms[8], ls[8], vs[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+          ms[r] = r < NS ? remote(pm_a + h * 4, r) : -INFINITY;
+          ls[r] = r < NS ? remote(pl_a + h * 4, r) : 0.f;
+          vs[r] = r < NS ? remote(part_a + i * 4, r) : 0.f;
+        }
+        float mn = -INFINITY, lt = 0.f, a = 0.f;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) mn = fmaxf(mn, ms[r]);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) lt += ms[r] == -INFINITY ? 0.f : ls[r] * exp2f(ms[r] - mn);
+        const float inv = 1.f / lt;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) a = fmaf(vs[r], ms[r] == -INFINITY ? 0.f : exp2f(ms[r] - mn) * inv, a);
+        p.out[((int64_t)b * H + gi * p.qpk + h) * HS + (i % HS)] = __float2bfloat16_rn(a);
+      }
+    }
+    // no CTA leaves (and frees its shared memory) before rank 0 has read it
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    return;
+  }
 
   // ---- last CTA of this (batch, group) merges the splits (protocol of attn_body.cuh) -----------------------------
   __threadfence();
@@ -282,9 +326,27 @@ __global__ void __launch_bounds__(128, 1) attn_decode_gqa_kernel(const AttnParam
 bool attn_decode_gqa_supported(int head_size, int qpk) { return head_size == kGqHS && qpk >= 2 && qpk <= kGqRows; }
 
 cudaError_t launch_attn_decode_gqa(const AttnParams& p, dim3 grid, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(attn_decode_gqa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGqSmem);
+  const bool cluster = grid.x >= 2 && grid.x <= 8;
+  auto kernel = cluster ? attn_decode_gqa_kernel<true> : attn_decode_gqa_kernel<false>;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGqSmem);
   if (e != cudaSuccess) return e;
-  return launch(attn_decode_gqa_kernel, grid, dim3(128), (size_t)kGqSmem, st, p);
+  if (!cluster) return launch(kernel, grid, dim3(128), (size_t)kGqSmem, st, p);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(128);
+  cfg.dynamicSmemBytes = (size_t)kGqSmem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = grid.x;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_pdl.load(std::memory_order_relaxed) ? 2 : 1;
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return cudaLaunchKernelEx(&cfg, kernel, p);
 }
 
 }  // namespace b200

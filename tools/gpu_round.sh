@@ -1,4 +1,6 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests/test_gpu_checkpoint.py -m gpu -x -q > gpurun_out/pytest_ckpt.log 2>&1; echo "pytest rc=$?"; grep -v "^DEBUG\|Deprecat\|warnings.warn" gpurun_out/pytest_ckpt.log | tail -30
+timeout 1200 python -m pytest tests -m gpu -x -q -k "attn or program or model or sample" > gpurun_out/pytest_attn.log 2>&1; echo "pytest rc=$?"; grep -v "^DEBUG\|Deprec\|warnings.warn" gpurun_out/pytest_attn.log | tail -12
+timeout 300 python tools/attn_bench.py 2>&1 | cut -c1-130 | grep -v "b4\|b16"
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; cut -c1-200 gpurun_out/bench_default.json; tail -3 gpurun_out/bench_default.err
