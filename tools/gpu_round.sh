@@ -1,6 +1,5 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests -m gpu -x -q -k "attn or program or model or sample" > gpurun_out/pytest_attn.log 2>&1; echo "pytest rc=$?"; grep -v "^DEBUG\|Deprec\|warnings.warn" gpurun_out/pytest_attn.log | tail -12
-timeout 300 python tools/attn_bench.py 2>&1 | cut -c1-130 | grep -v "b4\|b16"
-timeout 600 python bench.py --no-cpu-baseline > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; cut -c1-200 gpurun_out/bench_default.json; tail -3 gpurun_out/bench_default.err
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:qgemv_stream --launch-skip 3 -c 1 -o gpurun_out/prof_qgemv_int4 -f python tools/gemv_bench.py --qt int4 --l2pf 0 --reps 2 > gpurun_out/ncu_int4.log 2>&1; echo "rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:qgemv_stream --launch-skip 3 -c 1 -o gpurun_out/prof_qgemv_nf4 -f python tools/gemv_bench.py --qt nf4 --l2pf 0 --reps 2 > gpurun_out/ncu_nf4.log 2>&1; echo "rc=$?"
