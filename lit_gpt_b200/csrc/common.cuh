@@ -84,6 +84,33 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// int4 zero-point term: xsum[b * nkb + kb] = sum of the 64 bf16 activations of k-block kb of row b (rows in shared memory,
+// `xstride` elements apart).  Eight lanes per k-block, each reading four words whose order is rotated by the k-block's
+// slot so that the four k-blocks of a warp hit distinct banks (the one-thread-per-k-block loop this replaces had every lane
+// of a warp on the same bank: 32-way conflicts, ~1 us per launch), then a fixed shuffle tree: deterministic.
+// All NT threads must call it (NT a multiple of 32); the caller barriers afterwards.
+template <int NT>
+__device__ __forceinline__ void xsum_blocks(const __nv_bfloat16* x_s, int xstride, int B, int nkb, float* xsum_s, int tid) {
+  const int total = B * nkb, sub = tid & 7, slot = tid >> 3;
+  for (int base = 0; base < total; base += NT / 8) {
+    const int i = base + slot;
+    float s = 0.f;
+    if (i < total) {
+      const int b = i / nkb, kb = i % nkb;
+      const uint32_t* px = reinterpret_cast<const uint32_t*>(x_s + b * xstride + kb * 64);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t w = px[sub + 8 * ((j + slot) & 3)];
+        s += bf16lo(w) + bf16hi(w);
+      }
+    }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (sub == 0 && i < total) xsum_s[i] = s;
+  }
+}
+
 // streaming 128-bit / 64-bit loads that bypass L1 allocation (weights are read exactly once)
 __device__ __forceinline__ uint4 ldg_stream_v4(const void* p) {
   uint4 r;

@@ -319,14 +319,7 @@ __global__ void __launch_bounds__(kDThreadsAll, 1) decode_step_kernel(const Step
         }
         asm volatile("bar.sync 1, %0;" ::"n"(kDConsumers) : "memory");  // x_s is published
         if (INT4) {       // per (batch row, k-block) activation sums for the zero-point term
-          for (int i = tid; i < B * nkb; i += kDConsumers) {
-            const int b = i / nkb, kb = i % nkb;
-            const uint32_t* px = reinterpret_cast<const uint32_t*>(x_s + b * xstride + kb * 64);
-            float s = 0.f;
-#pragma unroll 8
-            for (int j = 0; j < 32; ++j) s += bf16lo(px[j]) + bf16hi(px[j]);
-            xsum_s[i] = s;
-          }
+          xsum_blocks<kDConsumers>(x_s, xstride, B, nkb, xsum_s, tid);
           asm volatile("bar.sync 1, %0;" ::"n"(kDConsumers) : "memory");
         }
       }

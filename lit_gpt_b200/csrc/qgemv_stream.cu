@@ -317,14 +317,7 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     }
   }
   if (INT4) {       // per (batch row, k-block) activation sums for the zero-point term
-    for (int i = tid; i < B * p.nkb; i += kConsumers) {
-      const int b = i / p.nkb, kb = i % p.nkb;
-      const uint32_t* px = reinterpret_cast<const uint32_t*>(x_s + b * p.xstride + kb * 64);
-      float s = 0.f;
-#pragma unroll 8
-      for (int j = 0; j < 32; ++j) s += bf16lo(px[j]) + bf16hi(px[j]);
-      xsum_s[i] = s;
-    }
+    xsum_blocks<kConsumers>(x_s, p.xstride, B, p.nkb, xsum_s, tid);
     asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
   }
 
