@@ -213,12 +213,15 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
     return;
   }
   // ================================== CONSUMER WARPS ===============================================================
-  for (int i = tid; i < (INT4 ? 0 : 256 * 32); i += kConsumers) {
-    const int e = i >> 5, l = i & 31;
-    float lo, hi;
-    if (INT4) { lo = (float)(e & 15); hi = (float)(e >> 4); }                      // (unused: int4 has no table)
-    else { lo = code_value(p.qtype, e >> 4); hi = code_value(p.qtype, e & 15); }   // even element = HIGH nibble
-    lut[e * 64 + l] = pack_bf16(lo, hi);
+  if (!INT4) {
+    // table entry e = warp + 16 k, lane slot `lane`: element 0 (low half) = code[e >> 4] = code[k], element 1 = code[e & 15] =
+    // code[warp] (even element = HIGH nibble).  Sixteen independent constant loads + stores per thread, fully unrolled: the
+    // fill is on every SM's critical path between two kernels (a rolled loop with two dependent indexed constant loads per
+    // iteration cost ~0.8 us per launch)
+    const float* cb = p.qtype == B200_Q_NF4 ? kNF4 : kFP4;
+    const float mine = cb[warp];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) lut[(warp + 16 * k) * 64 + lane] = pack_bf16(cb[k], mine);
   }
   // RMSNorm weights are constants: fetch this thread's first chunks BEFORE waiting for the previous kernel, so their
   // global-load latency is off the critical path between the two kernels
