@@ -488,22 +488,22 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   int u = u0, r = 0, it = 0;
   bool has1 = p.swiglu || u + 1 < u1;
   if (total > 0) read_stage(0, c0, c1, cs0, cs1);
-  for (int i = 0; i < total; ++i) {
+  // One round; the stage registers ping-pong between two sets (the loop below is unrolled by two) so that handing the
+  // prefetched stage over costs no register moves.
+  auto do_round = [&](const int i, uint4 (&pa0)[KPU], uint4 (&pa1)[KPU], uint2& pas0, uint2& pas1, uint4 (&pb0)[KPU], uint4 (&pb1)[KPU],
+                      uint2& pbs0, uint2& pbs1) {
     int nu_ = u, nr = r + 1;  // position of round i+1
     if (nr == nrounds) { nr = 0; nu_ = u + ustep; }
     const bool nhas1 = p.swiglu || nu_ + 1 < u1;
-    if (i + 1 < total) read_stage(nr, n0, n1, ns0, ns1);
+    if (i + 1 < total) read_stage(nr, pb0, pb1, pbs0, pbs1);
     const int ku = r * kCW + warp;
     if (ku < nku_c) {
 #pragma unroll
-      for (int b = 0; b < KPU; ++b) compute(c0[b], c1[b], cs0, cs1, ku * KPU + b);
+      for (int b = 0; b < KPU; ++b) compute(pa0[b], pa1[b], pas0, pas1, ku * KPU + b);
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(bars_a + (kMaxStages + rs) * 8);  // round i's stage: read one iteration ago
     if (++rs == S) rs = 0;
-#pragma unroll
-    for (int b = 0; b < KPU; ++b) { c0[b] = n0[b]; c1[b] = n1[b]; }
-    cs0 = ns0; cs1 = ns1;
     if (nr == 0) {
       // ---- end of a step: reduce the 16 k-slices through shared memory (double-buffered: one barrier per step) ---
       float* rbuf = red + (RED_BUFS == 2 ? (it & 1) : 0) * RED_ONE + warp * (2 * 16 * COLS);
@@ -544,6 +544,10 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
       ++it;
     }
     u = nu_; r = nr; has1 = nhas1;
+  };
+  for (int i = 0; i < total; i += 2) {
+    do_round(i, c0, c1, cs0, cs1, n0, n1, ns0, ns1);
+    if (i + 1 < total) do_round(i + 1, n0, n1, ns0, ns1, c0, c1, cs0, cs1);
   }
 }
 
