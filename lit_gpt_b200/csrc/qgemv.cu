@@ -112,10 +112,59 @@ __device__ __forceinline__ float generic_weight(const GenericParams& p, int m, i
 }
 
 __global__ void __launch_bounds__(256) qgemv_generic_kernel(GenericParams p) {
+  __shared__ float s_code[16];
+  if (threadIdx.x < 16 && p.qtype != B200_Q_INT4) s_code[threadIdx.x] = code_value(p.qtype, threadIdx.x);
   griddep_wait();
+  __syncthreads();
   const int lane = threadIdx.x & 31;
   const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
   const int nmat = p.epilogue == B200_EPI_SWIGLU ? 2 : 1;
+  // 4-bit code books with K a multiple of 8 (e.g. a row-parallel tensor-parallel shard whose K is not a multiple of the
+  // 64-element block, so that blocks straddle rows and the tiled layout does not apply): eight weights per lane and
+  // step -- one 32-bit load of packed codes, one absmax (eight aligned elements never cross a block), one 128-bit load of
+  // activations -- instead of one byte load per weight.  Same value per weight as below: bf16(code * absmax).
+  const bool vec8 = p.qtype != B200_Q_INT4 && nmat == 1 && (p.K & 7) == 0 && (p.blocksize & 7) == 0 &&
+                    ((reinterpret_cast<uintptr_t>(p.x) & 15) == 0) && ((reinterpret_cast<uintptr_t>(p.w[0]) & 3) == 0);
+  if (vec8) {
+    for (int64_t n = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); n < p.N; n += warps_total) {
+      float acc[16];
+#pragma unroll
+      for (int bb = 0; bb < 16; ++bb) acc[bb] = 0.f;
+      for (int64_t k = (int64_t)lane * 8; k < p.K; k += 256) {
+        const int64_t e = n * p.K + k;
+        const uint32_t wq = __ldg(reinterpret_cast<const uint32_t*>(p.w[0] + (e >> 1)));
+        const float am = __uint_as_float(__ldg(p.s[0] + e / p.blocksize));
+        float w[8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {  // byte j holds elements 2j (high nibble) and 2j + 1 (low nibble)
+          const uint32_t by = (wq >> (8 * j)) & 0xFFu;
+          w[2 * j] = round_bf16(s_code[by >> 4] * am);
+          w[2 * j + 1] = round_bf16(s_code[by & 15] * am);
+        }
+#pragma unroll
+        for (int bb = 0; bb < 16; ++bb) {
+          if (bb >= p.batch) break;
+          const uint4 xv = *reinterpret_cast<const uint4*>(p.x + (int64_t)bb * p.K + k);
+          const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+          float a = acc[bb];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { a = fmaf(w[2 * j], bf16lo(xw[j]), a); a = fmaf(w[2 * j + 1], bf16hi(xw[j]), a); }
+          acc[bb] = a;
+        }
+      }
+#pragma unroll
+      for (int bb = 0; bb < 16; ++bb) {
+        if (bb >= p.batch) break;
+        const float v = warp_sum(acc[bb]);
+        if (lane == 0) {
+          GemvParams q{};
+          q.epilogue = p.epilogue; q.bias = p.bias; q.bias2 = p.bias2; q.residual = p.residual; q.y = p.y; q.N = p.N;
+          epilogue_store(q, n, bb, v, 0.f);
+        }
+      }
+    }
+    return;
+  }
   for (int64_t n = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); n < p.N; n += warps_total) {
     for (int b0 = 0; b0 < p.batch; b0 += 4) {
       float acc[2][4] = {};

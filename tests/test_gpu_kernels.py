@@ -126,7 +126,7 @@ def test_qgemv_tuning_variants_agree(K, ks, occ):
 
 
 @pytest.mark.parametrize("qt", ["nf4", "int4"])
-@pytest.mark.parametrize("N,Kdim,B", [(86, 32, 1), (33, 100, 2), (352, 96, 16), (7, 8, 1)])
+@pytest.mark.parametrize("N,Kdim,B", [(86, 32, 1), (33, 100, 2), (352, 96, 16), (7, 8, 1), (512, 1376, 1), (48, 1376, 5)])  # 1376 = 11008 / 8: TP-8 shard
 def test_qgemv_generic_path_odd_shapes(K, qt, N, Kdim, B):
     w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, B, qt, seed=N)
     y = K.qgemv(x.cuda(), packed, scale, N, Kdim, qt, bs)
