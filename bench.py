@@ -381,6 +381,10 @@ def run_ours(args) -> None:
 
 
 def main() -> None:
+    # stdout carries exactly one JSON line: NCCL's own banner / debug lines (when the box sets NCCL_DEBUG) go to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":  # the version banner is printf'd to stdout whatever the file is
+        os.environ["NCCL_DEBUG"] = "WARN"
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=256)
