@@ -18,6 +18,7 @@
 // Prologue: residual add + RMSNorm of the activation (lit_gpt/rmsnorm.py:19-25, model.py:591) into shared memory.
 // Epilogue: bias / residual add / SwiGLU with the reference's bf16 rounding points (lit_gpt/model.py:712-716).
 #include "common.cuh"
+#include "qgemv_v4.cuh"
 
 namespace b200 {
 
@@ -570,11 +571,13 @@ using namespace b200;
 
 extern "C" {
 
-size_t b200_qgemv_tiled_workspace_bytes(void) { return 256; }  // no workspace is needed any more (kept for ABI)
+size_t b200_qgemv_tiled_workspace_bytes(void) { return qgemv_v4_workspace_bytes(); }  // stream-K partial sums + flags (self-cleaning)
 
 int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch) {
   g_stream_depth = depth;
   g_stream_occ = ctas_per_sm;
+  // development knobs: 10 = never split entities, 11 = always, 12 = no register-resident activations
+  qgemv_v4_tune(ctas_per_sm == 11 ? 1 : ctas_per_sm == 10 ? 0 : -1, ctas_per_sm == 12 ? 0 : 1);
   g_stream_pf = l2_prefetch;
   return B200_OK;
 }
@@ -595,6 +598,25 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
                    reinterpret_cast<uintptr_t>(a->delta) | reinterpret_cast<uintptr_t>(a->x_out) |
                    reinterpret_cast<uintptr_t>(a->norm_weight) | reinterpret_cast<uintptr_t>(a->prefetch)) & 15) == 0,
                  "b200_qgemv_tiled: pointers must be 16-byte aligned");
+
+  if (a->tp) {
+    const b200_tp_handoff* h = a->tp;
+    B200_CHECK_ARG(h->world >= 2 && h->world <= 8 && h->rank >= 0 && h->rank < h->world, "b200_qgemv_tiled: tp world %d / rank %d out of range", h->world, h->rank);
+    B200_CHECK_ARG(!(h->slots && a->delta), "b200_qgemv_tiled: tp slots replace delta (pass delta = NULL)");
+    B200_CHECK_ARG(!(h->send_seq && a->epilogue == B200_EPI_SWIGLU), "b200_qgemv_tiled: the SWIGLU pair is column-parallel: nothing to hand off");
+    if (h->send_seq)
+      for (int r = 0; r < h->world; ++r)
+        B200_CHECK_ARG(h->peer_y[r] && (reinterpret_cast<uintptr_t>(h->peer_y[r]) & 3) == 0, "b200_qgemv_tiled: tp producer needs a 4-byte aligned peer_y for every rank");
+    if (h->slots)
+      B200_CHECK_ARG(h->recv_seq && h->recv_done && h->slot_stride >= (int64_t)a->batch * a->K * 4 && h->slot_stride % 16 == 0 &&
+                         (reinterpret_cast<uintptr_t>(h->slots) & 15) == 0,
+                     "b200_qgemv_tiled: tp consumer needs recv_seq, recv_done and 16-byte aligned slots of >= batch * K * 4 bytes");
+  }
+  // stream-K kernel (qgemv_v4.cu) unless forced off (tune depth 98) or the shape is outside its plan
+  if (g_stream_depth.load() != 98) {
+    const int rc = qgemv_v4_launch(a, g_stream_depth.load() == 99 ? 1 : 0, (cudaStream_t)stream);
+    if (rc != B200_ERR_UNSUPPORTED) return rc;
+  }
 
   StreamParams p{};
   const bool swiglu = a->epilogue == B200_EPI_SWIGLU;

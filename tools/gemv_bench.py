@@ -34,6 +34,7 @@ def main() -> None:
     ap.add_argument("--kernel", choices=["tiled", "ref"], default="tiled")
     ap.add_argument("--depth", type=int, default=0)
     ap.add_argument("--l2pf", type=int, default=1)
+    ap.add_argument("--tiny", action="store_true")
     args = ap.parse_args()
 
     from lit_gpt_b200 import Config
@@ -44,6 +45,8 @@ def main() -> None:
     qkv = (c.n_head + 2 * c.n_query_groups) * c.head_size
     shapes = [("attn.attn+norm", qkv, d, "norm"), ("attn.proj+res", d, d, "res"), ("fc_1|fc_2 swiglu+norm", I, d, "swiglu"),
               ("mlp.proj+res", d, I, "res"), ("lm_head+norm", V, d, "norm")]
+    if args.tiny:  # one tile per SM: the time of such a launch is the fixed cost of a kernel boundary
+        shapes += [("tiny+norm", 148 * 16, d, "norm"), ("tiny+res", 148 * 16, d, "res")]
     dev = torch.device("cuda")
     K.set_pdl(bool(args.pdl))
     K.qgemv_tune(args.ks, args.occ)
@@ -54,7 +57,7 @@ def main() -> None:
     for name, N, Kd, kind in shapes:
         nmat = 2 if kind == "swiglu" else 1
         bytes_alg = nmat * N * Kd * (0.5 + (4 / 64 if args.qt != "int4" else 4 / 128))
-        copies = max(2, int(300e6 // bytes_alg) + 1)
+        copies = min(64, max(2, int(300e6 // bytes_alg) + 1))
         mats = []
         for i in range(copies * nmat):
             w = torch.empty(N, Kd, dtype=torch.bfloat16, device=dev).normal_(0, 0.02)
