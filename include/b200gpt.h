@@ -249,64 +249,6 @@ int b200_sample(const void* logits, int logits_dtype, int64_t vocab, float tempe
                 const void* noise, void* token_out, int token_is_int64, void* pos_inout, int pos_is_int64, void* history,
                 int64_t history_len, b200_stream_t stream);
 
-/* ---- persistent decode step: a whole T = 1 forward (embedding, every block, lm_head) as ONE kernel launch ------
- * Replaces the per-token call chain generate/base.py:44-47 -> lit_gpt/model.py:499-519 -> 572-593 (x n_layer).
- * The caller describes the step as a list of ops over its own device buffers; op i+1 may read anything op i
- * wrote (the kernel separates consecutive ops with a grid-wide barrier).  One persistent CTA per SM: a producer
- * warp streams the tiled weights of every GEMV op, in program order, through a shared-memory ring (TMA bulk
- * copies) and keeps streaming the NEXT op's weights while the consumers are still at a barrier / in attention,
- * so HBM never idles at op boundaries; the dequant table, mbarriers and ring are set up once per step.
- * All GEMV ops of a program share qtype and blocksize (nf4/fp4: 64, int4: 128). */
-enum b200_op_kind { B200_OP_GEMV = 0, B200_OP_ATTN = 1, B200_OP_EMBED = 2 };
-typedef struct b200_step_op {
-  int32_t kind;              /* b200_op_kind */
-  int32_t epilogue;          /* GEMV: b200_epilogue */
-  int64_t N, K;              /* GEMV: weight (N, K); EMBED: table (N rows, K = dim) */
-  const void* w;             /* GEMV: tiled weights (b200_tile_4bit); EMBED: bf16 table */
-  const void* w2;            /* GEMV SWIGLU: second tiled matrix */
-  const void* x;             /* GEMV: activation (batch, K) bf16; ATTN: qkv (batch, (n_head + 2 n_groups) * hs) bf16; EMBED: token ids */
-  const void* delta;         /* GEMV: optional bf16 (batch, K) added to x in the prologue */
-  void* x_out;               /* GEMV: optional, receives x + delta */
-  const void* norm_weight;   /* GEMV: optional RMSNorm weight (K) bf16 */
-  const void* bias;          /* GEMV: optional bf16 (N) */
-  const void* bias2;         /* GEMV SWIGLU: optional bias of w2 */
-  const void* residual;      /* GEMV RESIDUAL: bf16 (batch, N) */
-  void* y;                   /* GEMV: (batch, N) bf16; ATTN: (batch, n_head * hs) bf16; EMBED: (batch, K) bf16 */
-  float norm_eps;
-  int32_t idx_is_int64;      /* EMBED */
-  /* ATTN: same meaning as b200_attn_decode_args */
-  int32_t table_dtype, table_preselected, rope_n_elem, pos_is_int64;
-  int32_t n_head, n_groups, head_size, max_seq, num_splits;
-  int32_t reserved;
-  const void* cos;
-  const void* sin;
-  const void* pos;
-  void* k_cache;
-  void* v_cache;
-  void* workspace;           /* ATTN split partials: b200_attn_decode_workspace_bytes(batch, n_head, hs, 64), zeroed once by the caller */
-} b200_step_op;
-
-typedef struct b200_decode_program {
-  const b200_step_op* ops_host;  /* n_ops ops, host memory (validated on every call: cheap) */
-  const b200_step_op* ops_dev;   /* the same ops in device memory (copied there by the caller, or by b200_decode_program_upload) */
-  int32_t n_ops;
-  int32_t batch;                 /* 1..16 */
-  int32_t qtype;                 /* b200_qtype of every GEMV op */
-  int32_t blocksize;
-  void* sync;                    /* device, owned by the program: [0, 256) barrier counter + error flag; beyond that an optional
-                                    trace area of 64 bytes per op (see b200_decode_step_tune) */
-  int64_t sync_bytes;            /* >= 256 */
-} b200_decode_program;
-
-/* validates the ops and copies them host -> device (async on `stream`; ops_host must stay alive until it ran) */
-int b200_decode_program_upload(const b200_decode_program* prog, b200_stream_t stream);
-/* one decode step = one memset node + ONE kernel launch on `stream` (graph-capturable) */
-int b200_decode_step(const b200_decode_program* prog, b200_stream_t stream);
-/* tuning / experiments: L2 look-ahead of the weight stream in KB per CTA (0 = off; default 0); trace != 0 makes CTA 0
- * record clock64() at 6 points of every op (op start, activations staged, main loop done, barrier arrived, barrier
- * passed, spare) into sync[256 + 64 * op] when sync_bytes allows. */
-int b200_decode_step_tune(int lookahead_kb, int trace);
-
 /* ---- prefill GEMM: y (M, N) = x (M, K) · dequant(W)^T, tcgen05/TMEM mainloop (replaces dequantize_4bit +
  *      F.linear for T > 1 at the same call sites).  Implemented in csrc/qgemm_tcgen05.cu. */
 typedef struct b200_qgemm_args {

@@ -61,27 +61,6 @@ class AttnDecodeArgs(ctypes.Structure):
     ]
 
 
-class StepOp(ctypes.Structure):
-    """b200_step_op (include/b200gpt.h): one op of a persistent decode-step program."""
-    _fields_ = [
-        ("kind", ctypes.c_int32), ("epilogue", ctypes.c_int32), ("N", c_int64), ("K", c_int64),
-        ("w", c_void_p), ("w2", c_void_p), ("x", c_void_p), ("delta", c_void_p), ("x_out", c_void_p),
-        ("norm_weight", c_void_p), ("bias", c_void_p), ("bias2", c_void_p), ("residual", c_void_p), ("y", c_void_p),
-        ("norm_eps", c_float), ("idx_is_int64", ctypes.c_int32),
-        ("table_dtype", ctypes.c_int32), ("table_preselected", ctypes.c_int32), ("rope_n_elem", ctypes.c_int32), ("pos_is_int64", ctypes.c_int32),
-        ("n_head", ctypes.c_int32), ("n_groups", ctypes.c_int32), ("head_size", ctypes.c_int32), ("max_seq", ctypes.c_int32),
-        ("num_splits", ctypes.c_int32), ("reserved", ctypes.c_int32),
-        ("cos", c_void_p), ("sin", c_void_p), ("pos", c_void_p), ("k_cache", c_void_p), ("v_cache", c_void_p), ("workspace", c_void_p),
-    ]
-
-
-class DecodeProgram(ctypes.Structure):
-    _fields_ = [
-        ("ops_host", ctypes.POINTER(StepOp)), ("ops_dev", c_void_p), ("n_ops", ctypes.c_int32), ("batch", ctypes.c_int32),
-        ("qtype", ctypes.c_int32), ("blocksize", ctypes.c_int32), ("sync", c_void_p), ("sync_bytes", c_int64),
-    ]
-
-
 class QGemmArgs(ctypes.Structure):
     _fields_ = [
         ("packed", c_void_p), ("scale", c_void_p), ("qtype", c_int), ("blocksize", c_int),
@@ -118,9 +97,6 @@ _SIGNATURES = {
     "b200_qgemv_tiled": (c_int, [ctypes.POINTER(QGemvTiledArgs), c_void_p]),
     "b200_qgemv_tiled_workspace_bytes": (c_size_t, []),
     "b200_qgemv_tiled_tune": (c_int, [c_int, c_int, c_int]),
-    "b200_decode_program_upload": (c_int, [ctypes.POINTER(DecodeProgram), c_void_p]),
-    "b200_decode_step": (c_int, [ctypes.POINTER(DecodeProgram), c_void_p]),
-    "b200_decode_step_tune": (c_int, [c_int, c_int]),
     "b200_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
     "b200_attn_decode_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_attn_decode": (c_int, [ctypes.POINTER(AttnDecodeArgs), c_void_p]),

@@ -45,12 +45,15 @@ def save_quantized(model: nn.Module, path: Union[str, os.PathLike]) -> None:
 def load_quantized(model: nn.Module, path: Union[str, os.PathLike], device: Union[str, torch.device] = "cuda") -> nn.Module:
     """``model``: a GPT whose Linears are ``QLinear`` of the checkpoint's mode (``fabric.init_module`` / ``convert_module``), on
     meta, CPU or CUDA, already sharded if the checkpoint is a TP shard.  Returns the model on ``device`` ready to decode."""
-    st = torch.load(str(path), map_location="cpu", weights_only=False)
+    st = torch.load(str(path), map_location="cpu", weights_only=True)  # tensors / str / int / float / list / dict only
     if not isinstance(st, dict) or st.get("format") != FORMAT:
         raise B200Error(f"{path}: not a {FORMAT} checkpoint")
     world = int(getattr(model, "tp_world_size", 1))
     if st["tp"]["world"] != world:
         raise B200Error(f"checkpoint was written for tensor-parallel world size {st['tp']['world']}, the model is set up for {world}")
+    rank = int(getattr(model, "tp_rank", 0))
+    if st["tp"]["rank"] != rank:
+        raise B200Error(f"checkpoint holds the shard of tensor-parallel rank {st['tp']['rank']}, this process is rank {rank}")
     dev = torch.device(device)
     mods = {n: m for n, m in model.named_modules() if isinstance(m, QLinear)}
     missing = sorted(set(mods) - set(st["packed"]))

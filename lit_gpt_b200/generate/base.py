@@ -18,6 +18,7 @@ import torch
 from lit_gpt_b200 import GPT, Config, QuantPrecision
 from lit_gpt_b200 import kernels as K
 from lit_gpt_b200.fabric import Fabric, seed_everything
+from lit_gpt_b200.quant import weight_epoch
 from lit_gpt_b200.utils import check_valid_checkpoint_dir, get_default_supported_precision, load_checkpoint
 
 EOS_POLL = 16
@@ -106,8 +107,9 @@ class DecodeGraph:
 
 def _decode_graph_for(model: GPT, temperature: float, top_k: Optional[int], dtype: torch.dtype) -> DecodeGraph:
     cache: Dict[Tuple, DecodeGraph] = model.__dict__.setdefault("_decode_graphs", {})
-    kv_id = id(model.transformer.h[0].attn.kv_cache.k) if len(model.transformer.h) else 0
-    key = (temperature, top_k, dtype, model.max_seq_length, kv_id)
+    # a captured graph bakes in raw device pointers: key on the addresses themselves (id() of a freed tensor can be reused)
+    kv = [(b.attn.kv_cache.k.data_ptr(), b.attn.kv_cache.v.data_ptr()) for b in model.transformer.h]
+    key = (temperature, top_k, dtype, model.max_seq_length, tuple(kv), model.cos.data_ptr(), model.sin.data_ptr(), weight_epoch())
     dg = cache.get(key)
     if dg is None:
         cache.clear()  # graphs pin the kv-cache buffers they were captured with

@@ -83,6 +83,7 @@ def tensor_parallel(fabric: Any, model: GPT) -> GPT:
             raise ValueError(f"This {attr} value ({size}) is not evenly divisible by the world size ({world_size})")
         setattr(model.config, attr, size // world_size)
     model.tp_world_size = world_size
+    model.tp_rank = fabric.global_rank  # recorded in (and checked against) pre-quantized shard checkpoints
     model.tp_group = None  # default process group
     model._fused_plan = None
     return model

@@ -486,102 +486,3 @@ def launch_count() -> int:
 def qgemv_tune(ksteps: int = 0, ctas_per_sm: int = 0, force_generic: bool = False) -> None:
     C.load().b200_qgemv_tune(ksteps, ctas_per_sm, int(force_generic))
 
-
-# ---------------------------------------------------------------------------------------------------------
-# persistent decode step (b200_decode_step): a whole T = 1 forward as one kernel launch
-# ---------------------------------------------------------------------------------------------------------
-OP_GEMV, OP_ATTN, OP_EMBED = 0, 1, 2
-EPI_STORE, EPI_RESIDUAL, EPI_SWIGLU = 0, 1, 2
-
-
-def decode_step_tune(lookahead_kb: int = 0, trace: bool = False, debug: int = 0) -> None:
-    """L2 look-ahead of the weight stream per CTA in KB (0 = off); trace: CTA 0 records clock64() per op phase;
-    debug (experiments only): bit 0 = skip the dequant/MMA work, bit 1 = split every tile copy in four."""
-    C.check(C.load().b200_decode_step_tune(int(lookahead_kb), int(bool(trace)) | (int(debug) << 4)), "decode_step_tune")
-
-
-class DecodeProgram:
-    """Builder + handle for a ``b200_decode_program``: the op list of one decode step over fixed device buffers.
-
-    Every tensor handed to ``gemv`` / ``attn`` / ``embed`` is kept alive by the program; ``finalize()`` uploads the
-    ops, ``run()`` launches the step on the current stream (capturable in a CUDA graph)."""
-
-    def __init__(self, batch: int, quant_type: str, blocksize: int, device: torch.device) -> None:
-        self.batch, self.quant_type, self.blocksize, self.device = batch, quant_type, blocksize, device
-        self._ops: list = []
-        self._keep: list = []
-        self._prog: Optional[C.DecodeProgram] = None
-
-    def _p(self, t: Optional[torch.Tensor]) -> Optional[int]:
-        if t is None:
-            return None
-        C.require_cuda(t)
-        if not t.is_contiguous():
-            raise C.B200Error("decode program buffers must be contiguous")
-        self._keep.append(t)
-        return t.data_ptr()
-
-    def gemv(self, x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, y: torch.Tensor, *, tiled2: Optional[torch.Tensor] = None,
-             delta: Optional[torch.Tensor] = None, x_out: Optional[torch.Tensor] = None, norm_weight: Optional[torch.Tensor] = None,
-             norm_eps: float = 1e-5, bias: Optional[torch.Tensor] = None, bias2: Optional[torch.Tensor] = None,
-             residual: Optional[torch.Tensor] = None) -> None:
-        for name, t in (("x", x), ("y", y), ("delta", delta), ("x_out", x_out), ("norm_weight", norm_weight), ("bias", bias),
-                        ("bias2", bias2), ("residual", residual)):
-            if t is not None and t.dtype != torch.bfloat16:
-                raise C.B200Error(f"decode program gemv: {name} must be bfloat16")
-        if x.numel() != self.batch * K or y.numel() != self.batch * N:
-            raise C.B200Error("decode program gemv: x / y do not match (batch, K) / (batch, N)")
-        epi = EPI_SWIGLU if tiled2 is not None else (EPI_RESIDUAL if residual is not None else EPI_STORE)
-        self._ops.append(C.StepOp(kind=OP_GEMV, epilogue=epi, N=N, K=K, w=self._p(tiled), w2=self._p(tiled2), x=self._p(x),
-                                  delta=self._p(delta), x_out=self._p(x_out), norm_weight=self._p(norm_weight), bias=self._p(bias),
-                                  bias2=self._p(bias2), residual=self._p(residual), y=self._p(y), norm_eps=norm_eps))
-
-    def attn(self, qkv: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, pos: torch.Tensor, k_cache: torch.Tensor,
-             v_cache: torch.Tensor, out: torch.Tensor, n_head: int, n_groups: int, head_size: int, rope_n_elem: int,
-             num_splits: int = 0) -> None:
-        B, max_seq = k_cache.shape[0], k_cache.shape[2]
-        if B != self.batch or k_cache.dtype != torch.bfloat16 or qkv.dtype != torch.bfloat16 or out.dtype != torch.bfloat16:
-            raise C.B200Error("decode program attn: bf16 qkv/out and a (batch, n_query_groups, max_seq, head_size) bf16 cache are required")
-        if qkv.numel() != B * (n_head + 2 * n_groups) * head_size or out.numel() != B * n_head * head_size:
-            raise C.B200Error("decode program attn: qkv / out do not hold exactly one token per cached sequence")
-        if pos.dtype not in (torch.int64, torch.int32) or pos.numel() != 1:
-            raise C.B200Error("decode program attn: pos must be a single int32/int64 device scalar")
-        lib = C.load()
-        if num_splits <= 0:  # same rule as b200_attn_decode, with 4 sub-blocks per CTA as the parallelism target
-            sm = ctypes.c_int()
-            lib.b200_device_info(ctypes.byref(sm), ctypes.byref(ctypes.c_int()), ctypes.byref(ctypes.c_int()))
-            qpk = n_head // n_groups
-            qpk_t = 1 if qpk == 1 else (2 if qpk == 2 else (4 if qpk <= 4 else 8))
-            items = B * n_groups * ((qpk + qpk_t - 1) // qpk_t)
-            num_splits = max(1, min((2 * sm.value + items - 1) // items, (max_seq + 63) // 64, 64))
-        ws = _ws("attn_step", qkv.device, lib.b200_attn_decode_workspace_bytes(B, n_head, head_size, 64))
-        self._ops.append(C.StepOp(kind=OP_ATTN, x=self._p(qkv), y=self._p(out), cos=self._p(cos), sin=self._p(sin), pos=self._p(pos),
-                                  k_cache=self._p(k_cache), v_cache=self._p(v_cache), workspace=self._p(ws),
-                                  table_dtype=_table_code(cos), table_preselected=0, rope_n_elem=rope_n_elem,
-                                  pos_is_int64=int(pos.dtype == torch.int64), n_head=n_head, n_groups=n_groups, head_size=head_size,
-                                  max_seq=max_seq, num_splits=num_splits))
-
-    def embed(self, idx: torch.Tensor, wte: torch.Tensor, out: torch.Tensor) -> None:
-        if idx.dtype not in (torch.int64, torch.int32) or idx.numel() != self.batch or wte.dtype != torch.bfloat16:
-            raise C.B200Error("decode program embed: int32/int64 ids (one per sequence) and a bf16 table are required")
-        self._ops.append(C.StepOp(kind=OP_EMBED, N=wte.shape[0], K=wte.shape[1], w=self._p(wte), x=self._p(idx), y=self._p(out),
-                                  idx_is_int64=int(idx.dtype == torch.int64)))
-
-    def finalize(self) -> "DecodeProgram":
-        n = len(self._ops)
-        self._host = (C.StepOp * n)(*self._ops)
-        self._dev = torch.empty(ctypes.sizeof(C.StepOp) * n, dtype=torch.uint8, device=self.device)
-        self._sync = torch.zeros(256 + 64 * n, dtype=torch.uint8, device=self.device)
-        self._prog = C.DecodeProgram(ops_host=self._host, ops_dev=self._dev.data_ptr(), n_ops=n, batch=self.batch,
-                                     qtype=QTYPES[self.quant_type], blocksize=self.blocksize, sync=self._sync.data_ptr(), sync_bytes=self._sync.numel())
-        C.check(C.load().b200_decode_program_upload(ctypes.byref(self._prog), C.stream_ptr(self.device)), "decode_program_upload")
-        return self
-
-    def trace(self) -> torch.Tensor:
-        """(n_ops, 8) int64 clock64() stamps of CTA 0 from the last traced run (decode_step_tune(trace=True))."""
-        return self._sync[256:].view(torch.int64).view(-1, 8).cpu()
-
-    def run(self) -> None:
-        if self._prog is None:
-            raise C.B200Error("DecodeProgram.run() before finalize()")
-        C.check(C.load().b200_decode_step(ctypes.byref(self._prog), C.stream_ptr(self.device)), "decode_step")

@@ -125,14 +125,14 @@ class GPT(nn.Module):
         if self.mask_cache is None or self.mask_cache.size(3) != max_seq_length:
             self.mask_cache = build_mask_cache(max_seq_length, device)
         self._fused_plan = None
-        self.__dict__.pop("_decode_programs", None)
+        self.__dict__.pop("_decode_graphs", None)  # captured graphs pin the kv / table / weight buffers
 
     def clear_kv_cache(self) -> None:
         self.mask_cache = None
         for block in self.transformer.h:
             block.attn.kv_cache = None
         self._fused_plan = None
-        self.__dict__.pop("_decode_programs", None)
+        self.__dict__.pop("_decode_graphs", None)  # captured graphs pin the kv / table / weight buffers
 
     # ------------------------------------------------------------------------------------------------------
     # fused decode step
@@ -142,7 +142,7 @@ class GPT(nn.Module):
     def _apply(self, fn, recurse: bool = True):
         self._fused_plan = None  # device moves quantize the Linears: re-plan on the next forward
         self.__dict__.pop("_p2p", None)
-        self.__dict__.pop("_decode_programs", None)
+        self.__dict__.pop("_decode_graphs", None)  # captured graphs pin the kv / table / weight buffers
         return super()._apply(fn, recurse)
 
     def fused_decode_ready(self, idx: Optional[torch.Tensor] = None) -> bool:
@@ -221,75 +221,12 @@ class GPT(nn.Module):
         self.__dict__["_p2p"] = comm
         return comm or None
 
-    # ---- persistent decode step: the whole T = 1 forward as ONE kernel launch (csrc/decode_step.cu) ---------
-    # Experimental (off by default): measured 2.1 ms/step vs 1.73 ms for the PDL-chained per-op launches on
-    # Llama-2-7B nf4 -- the grid barrier + prologue per op (~3.4 us) costs more than a chained launch.
-    use_decode_program: bool = False
-
-    def _program_for(self, idx: torch.Tensor, input_pos: torch.Tensor) -> Optional[Any]:
-        """Build (once per set of static buffers) the op list of a decode step; None when the step is not covered."""
-        if not self.use_decode_program or self.tp_world_size > 1 or idx.size(0) > 16:
-            return None
-        progs = self.__dict__.setdefault("_decode_programs", {})
-        key = (idx.size(0), idx.dtype, input_pos.dtype)
-        if key in progs:
-            return progs[key]
-        if torch.cuda.is_current_stream_capturing():
-            return None  # programs are built (buffers allocated, ops uploaded) by an eager step before capture
-        c, B, dev = self.config, idx.size(0), idx.device
-        blocks = list(self.transformer.h)
-        lins = [self.lm_head] + [l for b in blocks for l in (b.attn.attn, b.attn.proj, b.mlp.fc_1, b.mlp.fc_2, b.mlp.proj)]
-        qt, bs = self.lm_head.quant_type, self.lm_head.blocksize
-        prog = None
-        if all(l.tiled is not None and l.quant_type == qt and l.blocksize == bs for l in lins) and input_pos.numel() == 1:
-            P = K.DecodeProgram(B, qt, bs, dev)
-
-            def new(n: int) -> torch.Tensor:
-                return torch.empty((B, n), dtype=torch.bfloat16, device=dev)
-
-            def gemv(q: QLinear, x: torch.Tensor, other: Optional[QLinear] = None, **kw: Any) -> torch.Tensor:
-                y = new(q.out_features)
-                P.gemv(x, q.tiled, q.out_features, q.in_features, y, tiled2=None if other is None else other.tiled, **kw)
-                return y
-
-            eps = c.norm_eps
-            x = new(c.n_embd)
-            # the program reads the token ids and the position from ITS OWN buffers (fixed addresses); callers'
-            # tensors are copied in unless they already are these buffers
-            idx_buf, pos_buf = torch.zeros_like(idx.reshape(B)), torch.zeros_like(input_pos.reshape(1))
-            P.embed(idx_buf, self.transformer.wte.weight, x)
-            input_pos = pos_buf
-            for block in blocks:
-                a, m, cache = block.attn, block.mlp, block.attn.kv_cache
-                qkv = gemv(a.attn, x, norm_weight=block.norm_1.weight, norm_eps=eps)
-                y = new(c.n_head * c.head_size)
-                P.attn(qkv, self.cos, self.sin, input_pos, cache.k, cache.v, y, c.n_head, c.n_query_groups, c.head_size, c.rope_n_elem)
-                x = gemv(a.proj, y, residual=x)
-                act = gemv(m.fc_1, x, other=m.fc_2, norm_weight=block.norm_2.weight, norm_eps=eps)
-                x = gemv(m.proj, act, residual=x)
-            logits = gemv(self.lm_head, x, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
-            try:
-                prog = (P.finalize(), logits, idx_buf, pos_buf)
-            except NotImplementedError:
-                prog = None  # e.g. batch x max(K) does not fit the kernel's shared-memory plan: use the chain
-        progs[key] = prog
-        return prog
-
     def _fused_decode(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
         """One token per sequence.  Same math as Block.forward / CausalSelfAttention.forward / LLaMAMLP.forward of
         the reference (model.py:572-593, 609-656, 712-716) with identical bf16 rounding points."""
         c = self.config
         B = idx.size(0)
         tp = self.tp_world_size > 1
-        prog = self._program_for(idx, input_pos)
-        if prog is not None:
-            if idx.data_ptr() != prog[2].data_ptr():
-                prog[2].copy_(idx.reshape(B))
-            if input_pos.data_ptr() != prog[3].data_ptr():
-                prog[3].copy_(input_pos.reshape(1))
-            prog[0].run()
-            logits = prog[1] if torch.cuda.is_current_stream_capturing() else prog[1].clone()
-            return logits.view(B, 1, -1)
         x = K.embedding(idx.view(B), self.transformer.wte.weight)  # (B, d_full)
         delta: Optional[torch.Tensor] = None
         eps = c.norm_eps

@@ -32,6 +32,20 @@ MODES = ("nf4", "nf4-dq", "fp4", "fp4-dq", "int8", "int4")
 GEMV_MAX_ROWS = 16
 
 
+# Captured decode graphs (generate/base.py) bake in the device pointers of the packed / tiled weights: every (re)quantisation
+# or packed import anywhere bumps this counter, and the graph cache keys on it.
+_WEIGHT_EPOCH = 0
+
+
+def bump_weight_epoch() -> None:
+    global _WEIGHT_EPOCH
+    _WEIGHT_EPOCH += 1
+
+
+def weight_epoch() -> int:
+    return _WEIGHT_EPOCH
+
+
 class QLinear(nn.Module):
     def __init__(self, in_features: int, out_features: int, bias: bool = True, device=None, dtype=None,
                  mode: str = "nf4", compute_dtype: torch.dtype = torch.bfloat16) -> None:
@@ -83,6 +97,7 @@ class QLinear(nn.Module):
         """Quantize the (CUDA, floating point) weight in place with the library's kernels."""
         if self.is_quantized:
             return
+        bump_weight_epoch()
         w = self.weight.data
         if not w.is_cuda:
             raise B200Error("QLinear quantizes on the GPU only (move the module to CUDA); there is no CPU path")
@@ -129,7 +144,7 @@ class QLinear(nn.Module):
         """CPU copies of exactly what ``quantize_`` produced (packed codes + statistics), keyed for ``import_packed``."""
         if not self.is_quantized:
             raise B200Error("export_packed: the module is not quantized yet")
-        out = {"mode": self.mode, "shape": tuple(self.quant_state[1]), "weight": self.weight.data.cpu()}
+        out = {"mode": self.mode, "shape": [int(d) for d in self.quant_state[1]], "weight": self.weight.data.cpu()}  # plain types: loads with weights_only=True
         if self.quant_type == "int8":
             out["SCB"] = self.SCB.cpu()
         elif self.quant_type == "int4":
@@ -155,6 +170,7 @@ class QLinear(nn.Module):
         dev = torch.device(device)
         if dev.type != "cuda":
             raise B200Error("import_packed: quantized modules live on CUDA only")
+        bump_weight_epoch()
         self.weight = nn.Parameter(st["weight"].to(dev), requires_grad=False)
         self.scales = self.qzeros = self.sz = self.tiled = self.absmax = self.SCB = None
         if self.quant_type == "int8":
