@@ -211,6 +211,18 @@ int b200_attn_decode(const b200_attn_decode_args* args, b200_stream_t stream);
  * thread-block cluster merging through distributed shared memory.  Returns the previous setting. */
 int b200_attn_decode_tune(int force_scalar);
 
+/* Allocation-free variant of b200_attn_decode.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments and results as b200_attn_decode, except that `workspace` / `workspace_bytes` are
+ * ignored: the split-K scratch lives in a static device array of b200_attn_decode_noalloc_max_bytes() = 4 MiB that every
+ * GPU loading the library holds until exit.  Shapes whose scratch need
+ * b200_attn_decode_workspace_bytes(batch, n_head, head_size, num_splits ? num_splits : 64) exceeds that are rejected with
+ * B200_ERR_UNSUPPORTED and a message.  No cudaMalloc / cudaFree / allocating routine is called; one cudaMemsetAsync on
+ * `stream` clears the counters that must start at zero.  All calls share the array: calls that overlap on the GPU
+ * (different streams, or different threads on different streams) race; calls on one stream are ordered and safe. */
+size_t b200_attn_decode_noalloc_max_bytes(void);
+int b200_attn_decode_noalloc(const b200_attn_decode_args* args, b200_stream_t stream);
+
 /* ---- prefill helper: RoPE + KV-cache write for T > 1 tokens at positions pos[0..T) (lit_gpt/model.py:624-649).
  * table_preselected = 1: cos/sin are (T, rope_n_elem) rows already gathered by input_pos; 0: full tables.
  * Writes roped q to q_out (batch, n_head, T, head_size) and the roped k / v rows into the GQA-native caches. */

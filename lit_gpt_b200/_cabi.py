@@ -101,6 +101,8 @@ _SIGNATURES = {
     "b200_attn_decode_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_attn_decode": (c_int, [ctypes.POINTER(AttnDecodeArgs), c_void_p]),
     "b200_attn_decode_tune": (c_int, [c_int]),
+    "b200_attn_decode_noalloc": (c_int, [ctypes.POINTER(AttnDecodeArgs), c_void_p]),
+    "b200_attn_decode_noalloc_max_bytes": (c_size_t, []),
     "b200_rope_kv_append": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                     c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_attn_prefill": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,

@@ -185,6 +185,52 @@ int b200_attn_decode(const b200_attn_decode_args* a, b200_stream_t stream) {
   return B200_OK;
 }
 
+// ---- allocation-free variant (no counterpart in the reference) ------------
+// Same kernel, same arguments, but the split-K scratch (partial (m, l, o) + ticket counters) lives in a file-scope
+// device array instead of a caller-provided workspace: for callers that cannot call cudaMalloc (CUDA graph capture,
+// tight serving loops, harnesses that forbid it).  Every GPU that loads the library holds the array until exit.
+// All calls share it: calls that overlap on the GPU (different streams) race; calls on one stream are ordered.
+#define B200_ATTN_NOALLOC_SCRATCH_BYTES (4u << 20)
+static __device__ __align__(256) unsigned char g_attn_noalloc_scratch[B200_ATTN_NOALLOC_SCRATCH_BYTES];
+
+size_t b200_attn_decode_noalloc_max_bytes(void) { return (size_t)B200_ATTN_NOALLOC_SCRATCH_BYTES; }
+
+int b200_attn_decode_noalloc(const b200_attn_decode_args* a, b200_stream_t stream) {
+  B200_CHECK_ARG(a != nullptr, "b200_attn_decode_noalloc: null args");
+  B200_CHECK_ARG(a->batch > 0 && a->n_head > 0 && a->head_size > 0, "b200_attn_decode_noalloc: bad shape");
+  B200_CHECK_ARG(a->num_splits >= 0 && a->num_splits <= 64, "b200_attn_decode_noalloc: num_splits %d out of range [0, 64]", a->num_splits);
+  // the split count is chosen inside b200_attn_decode when num_splits == 0: size for the most it can choose (64)
+  const size_t need = b200_attn_decode_workspace_bytes(a->batch, a->n_head, a->head_size, a->num_splits > 0 ? a->num_splits : 64);
+  if (need > (size_t)B200_ATTN_NOALLOC_SCRATCH_BYTES) {
+    set_error("b200_attn_decode_noalloc: batch %d x n_head %d x head_size %d x %d splits needs %zu bytes of scratch, the built-in array holds %zu "
+              "(use b200_attn_decode with a caller-owned workspace)", a->batch, a->n_head, a->head_size, a->num_splits > 0 ? a->num_splits : 64,
+              need, (size_t)B200_ATTN_NOALLOC_SCRATCH_BYTES);
+    return B200_ERR_UNSUPPORTED;
+  }
+  // the array's DEVICE address, resolved once per device with that device current (in host code the symbol's name is a
+  // host-side stand-in, not a device pointer)
+  static void* dev_ptr[64] = {};
+  static std::atomic<int> dev_ready[64] = {};
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_CHECK_ARG(dev >= 0 && dev < 64, "b200_attn_decode_noalloc: device ordinal %d not supported", dev);
+  if (!dev_ready[dev].load(std::memory_order_acquire)) {
+    void* ptr = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&ptr, g_attn_noalloc_scratch));
+    B200_CHECK_ARG(ptr != nullptr, "b200_attn_decode_noalloc: cudaGetSymbolAddress returned NULL");
+    dev_ptr[dev] = ptr;   // every thread resolves the same address: a benign race
+    dev_ready[dev].store(1, std::memory_order_release);
+  }
+  // the ticket counters at the start of the scratch must be zero when the kernel starts; the kernel cleans up after
+  // itself, but an earlier call with another shape (or an aborted one) may have left something: clear them on the stream
+  const size_t cnt_bytes = (((size_t)a->batch * a->n_head * sizeof(unsigned int)) + 255) & ~(size_t)255;
+  B200_CUDA(cudaMemsetAsync(dev_ptr[dev], 0, cnt_bytes, (cudaStream_t)stream));
+  b200_attn_decode_args b = *a;
+  b.workspace = dev_ptr[dev];
+  b.workspace_bytes = (size_t)B200_ATTN_NOALLOC_SCRATCH_BYTES;
+  return b200_attn_decode(&b, stream);
+}
+
 int b200_rope_kv_append(const void* qkv, const void* cos, const void* sin, int table_dtype, int table_preselected, int rope_n_elem, const void* pos,
                         int pos_is_int64, void* k_cache, void* v_cache, void* q_out, int batch, int T, int n_head, int n_groups,
                         int head_size, int max_seq, b200_stream_t stream) {
