@@ -173,6 +173,10 @@ size_t b200_qgemv_tiled_workspace_bytes(void);
 int b200_qgemv_tiled(const b200_qgemv_tiled_args* args, b200_stream_t stream);
 /* tuning: depth in {0(auto),2,4,6} items loaded ahead per warp; ctas_per_sm in {0(auto),1,2}; l2_prefetch 0/1 */
 int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch);
+/* diagnostics (no counterpart in the reference): the next `slots` b200_qgemv_tiled launches record eight per-CTA phase time
+ * stamps (%globaltimer, ns) into buf[slots][160][8] (uint64, device memory, caller-owned, zeroed by the caller);
+ * buf = NULL switches it off.  tools/trace_step.py turns them into the per-launch timeline quoted in DESIGN.md. */
+int b200_qgemv_tiled_trace(void* buf, int slots);
 
 /* ---- RMSNorm (replaces lit_gpt/rmsnorm.py:19-25 and the residual add at lit_gpt/model.py:591) ------------
  * y = RMSNorm(x (+ delta)) * weight; if sum_out != NULL it receives bf16(x + delta).  rows x dim, bf16. */

@@ -97,6 +97,7 @@ _SIGNATURES = {
     "b200_qgemv_tiled": (c_int, [ctypes.POINTER(QGemvTiledArgs), c_void_p]),
     "b200_qgemv_tiled_workspace_bytes": (c_size_t, []),
     "b200_qgemv_tiled_tune": (c_int, [c_int, c_int, c_int]),
+    "b200_qgemv_tiled_trace": (c_int, [c_void_p, c_int]),
     "b200_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
     "b200_attn_decode_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_attn_decode": (c_int, [ctypes.POINTER(AttnDecodeArgs), c_void_p]),

@@ -578,7 +578,13 @@ int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch) {
   g_stream_occ = ctas_per_sm;
   // development knobs: 10 = never split entities, 11 = always, 12 = no register-resident activations
   qgemv_v4_tune(ctas_per_sm == 11 ? 1 : ctas_per_sm == 10 ? 0 : -1, ctas_per_sm == 12 ? 0 : 1);
+  qgemv_v4_tune_occ2(ctas_per_sm == 13 ? 1 : 0);   // 13: int4 batch-1 as two co-resident CTAs per SM (experiment)
   g_stream_pf = l2_prefetch;
+  return B200_OK;
+}
+
+int b200_qgemv_tiled_trace(void* buf, int slots) {
+  qgemv_v4_set_trace(buf, slots);
   return B200_OK;
 }
 
@@ -614,7 +620,7 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   }
   // stream-K kernel (qgemv_v4.cu) unless forced off (tune depth 98) or the shape is outside its plan
   if (g_stream_depth.load() != 98) {
-    const int rc = qgemv_v4_launch(a, g_stream_depth.load() == 99 ? 1 : 0, (cudaStream_t)stream);
+    const int rc = qgemv_v4_launch(a, g_stream_depth.load() == 99 ? 1 : g_stream_depth.load() == 97 ? 3 : 0, (cudaStream_t)stream);  // 99: stream only, 97: prologue cycle stamps
     if (rc != B200_ERR_UNSUPPORTED) return rc;
   }
 

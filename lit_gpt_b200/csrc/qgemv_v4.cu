@@ -35,6 +35,7 @@ constexpr int kV4Threads = (kV4CW + 2) * 32;  // + producer + reducer
 constexpr int kV4Consumers = kV4CW * 32;
 constexpr int kV4MaxStages = 8;
 constexpr int kV4DynSmem = 227 * 1024;
+constexpr int kV4DynSmem2 = 110 * 1024;   // two co-resident CTAs per SM (experiment: consecutive launches overlap)
 constexpr int kV4MaxCtas = 160;
 constexpr size_t kV4WsData = 4096;            // workspace: [0] error word, [64 + 4 c] flag of CTA c, [4096 + 2048 c] partials of CTA c
 constexpr size_t kV4WsPerCta = 2048;
@@ -68,6 +69,7 @@ struct V4Params {
   int64_t tp_slot_stride;
   uint32_t* tp_recv_seq;
   uint32_t* tp_recv_done;
+  unsigned long long* trace;   // development: [cta][8] globaltimer stamps of this launch (NULL = off)
 };
 
 struct V4Plan {
@@ -77,7 +79,7 @@ struct V4Plan {
 
 // Shared-memory carve-up by ABSOLUTE shared-window address (the table must sit at a 64 KB aligned address so that
 // `byte << 8 | lane << 2 | table` is one PRMT).  Shared by the kernel and the host-side feasibility check.
-__host__ __device__ inline V4Plan v4_plan(uint32_t b0, int stage, int red_bytes, bool int4, int B, int nkb, int xstride, int gap) {
+__host__ __device__ inline V4Plan v4_plan(uint32_t b0, int stage, int red_bytes, bool int4, int B, int nkb, int xstride, int gap, int smem = kV4DynSmem) {
   V4Plan pl{};
   uint32_t off = (b0 + 127u) & ~127u;
   pl.bars = off; off += 256;
@@ -88,7 +90,7 @@ __host__ __device__ inline V4Plan v4_plan(uint32_t b0, int stage, int red_bytes,
   pl.xs = off; if (!gap) off += (((uint32_t)B * xstride * 2) + 127u) & ~127u;
   off = (off + 127u) & ~127u;
   pl.ringA = off;
-  const uint32_t end = b0 + kV4DynSmem;
+  const uint32_t end = b0 + (uint32_t)smem;
   if (int4) {
     pl.lut = 0; pl.ringC = end;
     pl.nA = off < end ? (int)((end - off) / stage) : 0; pl.nC = 0;
@@ -105,6 +107,18 @@ __host__ __device__ inline V4Plan v4_plan(uint32_t b0, int stage, int red_bytes,
   return pl;
 }
 
+__device__ __forceinline__ void v4_stamp(const V4Params& p, int ev) {
+  if (p.trace) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    p.trace[(size_t)blockIdx.x * 8 + ev] = t;
+  }
+}
+
+__device__ __forceinline__ void v4_stamp_cyc(const V4Params& p, int ev, long long c0) {
+  if (p.trace) p.trace[(size_t)blockIdx.x * 8 + ev] = (unsigned long long)(clock64() - c0);
+}
+
 __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -119,8 +133,8 @@ __device__ __forceinline__ float ld_cg_f32(const float* p) {
 // MODE 0: batch 1 (one accumulator column), MODE 1: batch <= 8, MODE 2: batch <= 16
 // XREG (batch 1, units per tile == consumer warps): a warp meets the same k-range in every unit, so its activation
 // fragments (and int4 block sums) stay in registers for the whole launch instead of being re-read from shared memory
-template <int RU, bool INT4, int MODE, bool XREG>
-__global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params p) {
+template <int RU, bool INT4, int MODE, bool XREG, int OCC = 1>
+__global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Params p) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   constexpr int NB = MODE == 2 ? 2 : 1;
   constexpr int COLS = 8 * NB;
@@ -135,7 +149,7 @@ __global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params 
   const uint32_t b0 = smem_u32(smem_raw);
   uint8_t* const sb = smem_raw - b0;           // generic pointer to shared-window address 0
   const int B = p.batch;
-  const V4Plan pl = v4_plan(b0, STAGE, NBUF * kV4CW * REDW * 4, INT4, B, p.nkb, p.xstride, p.gap);
+  const V4Plan pl = v4_plan(b0, STAGE, NBUF * kV4CW * REDW * 4, INT4, B, p.nkb, p.xstride, p.gap, OCC == 2 ? kV4DynSmem2 : kV4DynSmem);
   const int S = pl.S;
   if (S < 2) __trap();                         // the host sized the launch so that this cannot happen
   const uint32_t full_a = pl.bars, empty_a = pl.bars + 64, rfull_a = pl.bars + 128, rempty_a = pl.bars + 160;
@@ -152,8 +166,11 @@ __global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params 
   };
   const int u0 = range_start(cta), u1 = range_start(cta + 1);
   const int t_first = u0 / upt, t_last = (u1 - 1) / upt;   // flat tile range of this CTA (u1 > u0: the host keeps G <= entities / units)
+  // this consumer warp's first unit (index arithmetic with divisions: done here, off the post-dependency critical path)
+  const int u_first = u0 + warp, tf_first = u_first / upt, ku_first = u_first - tf_first * upt;
 
   if (tid == 0) {
+    v4_stamp(p, 0);
     for (int s = 0; s < kV4MaxStages; ++s) { mbar_init(full_a + s * 8, 1); mbar_init(empty_a + s * 8, kV4CW); }
     for (int s = 0; s < NBUF; ++s) { mbar_init(rfull_a + s * 8, kV4CW); mbar_init(rempty_a + s * 8, 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -185,6 +202,7 @@ __global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params 
         u += cnt;
         if (++ps == S) { ps = 0; pph ^= 1u; }
       }
+      if (p.debug != 3) v4_stamp(p, 6);
     }
     griddep_launch();
     return;
@@ -210,6 +228,7 @@ __global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params 
       }
     };
     const int e_first = t_first / TS, e_last = t_last / TS;
+    if (lane == 0 && p.debug != 3) v4_stamp(p, 7);
     int j = 0;  // tiles reduced so far (reduction-buffer sequence)
     for (int e = e_first; e <= e_last; ++e) {
       float val[2][NV];
@@ -312,6 +331,7 @@ __global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params 
         }
       }
     }
+    if (lane == 0) v4_stamp(p, 5);
     return;
   }
 
@@ -346,6 +366,8 @@ __global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params 
   }
   griddep_launch();
   griddep_wait();
+  if (tid == 0) v4_stamp(p, 1);
+  const long long c_rel = clock64();
 
   // ---- tensor-parallel consumer: the branch output is the sum of every rank's partial, written into this rank's slots by
   // the peers' epilogues (and its own) as self-validating packets; the expected tag comes from the buffer's local
@@ -354,78 +376,153 @@ __global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params 
   if (p.tp_slots) rtag = (__ldcg(p.tp_recv_seq) % 65535u) + 1u;
   // ---- activation prologue: (x + delta) -> optional RMSNorm -> bf16 rows in shared memory -------------------------
   const bool designated = cta == 0;
-  for (int b = 0; b < B; ++b) {
-    float ss = 0.f;
-    for (int c = tid; c < chunks; c += kV4Consumers) {
-      uint4 v = *reinterpret_cast<const uint4*>(p.x + (int64_t)b * p.K + c * 8);
-      if (p.delta || p.tp_slots) {
-        uint4 dv;
-        if (p.tp_slots) {  // sum of the ranks' partials in rank order (fp32), rounded once to bf16 like an all-reduced tensor
-          float acc8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-          for (int r = 0; r < p.tp_world; ++r) {
-            const uint32_t* sp = p.tp_slots + r * p.tp_slot_stride + (int64_t)b * p.K + c * 8;
-            uint4 pa, pb;
-            const long long t0 = clock64();
-            for (;;) {   // poll until all eight packets carry this hand-off's tag
-              asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(pa.x), "=r"(pa.y), "=r"(pa.z), "=r"(pa.w) : "l"(sp) : "memory");
-              asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(pb.x), "=r"(pb.y), "=r"(pb.z), "=r"(pb.w) : "l"(sp + 4) : "memory");
-              const bool ok = (pa.x >> 16) == rtag && (pa.y >> 16) == rtag && (pa.z >> 16) == rtag && (pa.w >> 16) == rtag &&
-                              (pb.x >> 16) == rtag && (pb.y >> 16) == rtag && (pb.z >> 16) == rtag && (pb.w >> 16) == rtag;
-              if (ok) break;
-              if (clock64() - t0 > 4000000000LL) {  // a peer died: raise the error word and carry on with what is there (no hang, no trap)
-                *reinterpret_cast<volatile uint32_t*>(p.ws) = 2u;
-                break;
-              }
-            }
-            acc8[0] += bf16lo(pa.x); acc8[1] += bf16lo(pa.y); acc8[2] += bf16lo(pa.z); acc8[3] += bf16lo(pa.w);
-            acc8[4] += bf16lo(pb.x); acc8[5] += bf16lo(pb.y); acc8[6] += bf16lo(pb.z); acc8[7] += bf16lo(pb.w);
-          }
-          dv = make_uint4(pack_bf16(acc8[0], acc8[1]), pack_bf16(acc8[2], acc8[3]), pack_bf16(acc8[4], acc8[5]), pack_bf16(acc8[6], acc8[7]));
-        } else {
-          dv = *reinterpret_cast<const uint4*>(p.delta + (int64_t)b * p.K + c * 8);
-        }
-        v.x = pack_bf16(bf16lo(v.x) + bf16lo(dv.x), bf16hi(v.x) + bf16hi(dv.x));
-        v.y = pack_bf16(bf16lo(v.y) + bf16lo(dv.y), bf16hi(v.y) + bf16hi(dv.y));
-        v.z = pack_bf16(bf16lo(v.z) + bf16lo(dv.z), bf16hi(v.z) + bf16hi(dv.z));
-        v.w = pack_bf16(bf16lo(v.w) + bf16lo(dv.w), bf16hi(v.w) + bf16hi(dv.w));
-        if (p.x_out && designated) *reinterpret_cast<uint4*>(p.x_out + (int64_t)b * p.K + c * 8) = v;
-      }
-      *reinterpret_cast<uint4*>(sb + xs_chunk(b, c)) = v;
-      const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+  if (B == 1 && !p.tp_slots && chunks <= 3 * kV4Consumers) {
+    // batch-1 fast path (the decode chain): every load of the row is in flight at once, ONE pass over registers, the
+    // sum of squares meets in shared memory with a single barrier and every thread derives rstd itself (same
+    // summation order and arithmetic as the general path below, so the two are bit-identical)
+    uint4 xv[3], dv[3];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { const float a = bf16lo(w4[i]), c2 = bf16hi(w4[i]); ss = fmaf(a, a, ss); ss = fmaf(c2, c2, ss); }
+    for (int i = 0; i < 3; ++i) {
+      const int c = tid + i * kV4Consumers;
+      if (c < chunks) xv[i] = *reinterpret_cast<const uint4*>(p.x + c * 8);
+    }
+    if (p.delta) {
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const int c = tid + i * kV4Consumers;
+        if (c < chunks) dv[i] = *reinterpret_cast<const uint4*>(p.delta + c * 8);
+      }
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const int c = tid + i * kV4Consumers;
+        if (c < chunks) {
+          uint4 v = xv[i];
+          v.x = pack_bf16(bf16lo(v.x) + bf16lo(dv[i].x), bf16hi(v.x) + bf16hi(dv[i].x));
+          v.y = pack_bf16(bf16lo(v.y) + bf16lo(dv[i].y), bf16hi(v.y) + bf16hi(dv[i].y));
+          v.z = pack_bf16(bf16lo(v.z) + bf16lo(dv[i].z), bf16hi(v.z) + bf16hi(dv[i].z));
+          v.w = pack_bf16(bf16lo(v.w) + bf16lo(dv[i].w), bf16hi(v.w) + bf16hi(dv[i].w));
+          if (p.x_out && designated) *reinterpret_cast<uint4*>(p.x_out + c * 8) = v;
+          xv[i] = v;
+        }
+      }
     }
     if (p.norm_w) {
-      ss = warp_sum(ss);
-      if (lane == 0) s_ssq[warp * 16 + b] = ss;
-    }
-  }
-  if (p.norm_w) {
-    asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
-    if (tid < B) {
-      float tot = 0.f;
+      float ss = 0.f;
 #pragma unroll
-      for (int w = 0; w < kV4CW; ++w) tot += s_ssq[w * 16 + tid];
-      s_rstd[tid] = rsqrtf(tot / (float)p.K + p.eps);
-    }
-    asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
-    for (int b = 0; b < B; ++b) {
-      const float rstd = s_rstd[b];
-      int ci = 0;
-      for (int c = tid; c < chunks; c += kV4Consumers, ++ci) {  // same thread owns the same chunk as above
-        uint4* px = reinterpret_cast<uint4*>(sb + xs_chunk(b, c));
-        uint4 v = *px;
-        const uint4 nw = ci == 0 ? nwreg[0] : ci == 1 ? nwreg[1] : ci == 2 ? nwreg[2] : *reinterpret_cast<const uint4*>(p.norm_w + c * 8);
-        // weight * (x * rstd), fp32, one cast (rmsnorm.py:24-25)
-        v.x = pack_bf16(bf16lo(nw.x) * (bf16lo(v.x) * rstd), bf16hi(nw.x) * (bf16hi(v.x) * rstd));
-        v.y = pack_bf16(bf16lo(nw.y) * (bf16lo(v.y) * rstd), bf16hi(nw.y) * (bf16hi(v.y) * rstd));
-        v.z = pack_bf16(bf16lo(nw.z) * (bf16lo(v.z) * rstd), bf16hi(nw.z) * (bf16hi(v.z) * rstd));
-        v.w = pack_bf16(bf16lo(nw.w) * (bf16lo(v.w) * rstd), bf16hi(nw.w) * (bf16hi(v.w) * rstd));
-        *px = v;
+      for (int i = 0; i < 3; ++i) {
+        if (tid + i * kV4Consumers < chunks) {
+          const uint32_t w4[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) { const float a = bf16lo(w4[q]), c2 = bf16hi(w4[q]); ss = fmaf(a, a, ss); ss = fmaf(c2, c2, ss); }
+        }
       }
+      ss = warp_sum(ss);
+      if (lane == 0) s_ssq[warp] = ss;
+      asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
+      const float4 q0 = *reinterpret_cast<const float4*>(s_ssq), q1 = *reinterpret_cast<const float4*>(s_ssq + 4),
+                   q2 = *reinterpret_cast<const float4*>(s_ssq + 8), q3 = *reinterpret_cast<const float4*>(s_ssq + 12);
+      float tot = 0.f;
+      tot += q0.x; tot += q0.y; tot += q0.z; tot += q0.w; tot += q1.x; tot += q1.y; tot += q1.z; tot += q1.w;
+      tot += q2.x; tot += q2.y; tot += q2.z; tot += q2.w; tot += q3.x; tot += q3.y; tot += q3.z; tot += q3.w;
+      const float rstd = rsqrtf(tot / (float)p.K + p.eps);
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        if (tid + i * kV4Consumers < chunks) {
+          const uint4 nw = nwreg[i];
+          uint4 v = xv[i];
+          // weight * (x * rstd), fp32, one cast (rmsnorm.py:24-25)
+          v.x = pack_bf16(bf16lo(nw.x) * (bf16lo(v.x) * rstd), bf16hi(nw.x) * (bf16hi(v.x) * rstd));
+          v.y = pack_bf16(bf16lo(nw.y) * (bf16lo(v.y) * rstd), bf16hi(nw.y) * (bf16hi(v.y) * rstd));
+          v.z = pack_bf16(bf16lo(nw.z) * (bf16lo(v.z) * rstd), bf16hi(nw.z) * (bf16hi(v.z) * rstd));
+          v.w = pack_bf16(bf16lo(nw.w) * (bf16lo(v.w) * rstd), bf16hi(nw.w) * (bf16hi(v.w) * rstd));
+          xv[i] = v;
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int c = tid + i * kV4Consumers;
+      if (c < chunks) *reinterpret_cast<uint4*>(sb + xs_chunk(0, c)) = xv[i];
+    }
+    if (tid == 0 && p.debug == 3) v4_stamp_cyc(p, 7, c_rel);
+  } else {
+    for (int b = 0; b < B; ++b) {
+      float ss = 0.f;
+      for (int c = tid; c < chunks; c += kV4Consumers) {
+        uint4 v = *reinterpret_cast<const uint4*>(p.x + (int64_t)b * p.K + c * 8);
+        if (p.delta || p.tp_slots) {
+          uint4 dv;
+          if (p.tp_slots) {  // sum of the ranks' partials in rank order (fp32), rounded once to bf16 like an all-reduced tensor
+            float acc8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            for (int r = 0; r < p.tp_world; ++r) {
+              const uint32_t* sp = p.tp_slots + r * p.tp_slot_stride + (int64_t)b * p.K + c * 8;
+              uint4 pa, pb;
+              const long long t0 = clock64();
+              for (;;) {   // poll until all eight packets carry this hand-off's tag
+                asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(pa.x), "=r"(pa.y), "=r"(pa.z), "=r"(pa.w) : "l"(sp) : "memory");
+                asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(pb.x), "=r"(pb.y), "=r"(pb.z), "=r"(pb.w) : "l"(sp + 4) : "memory");
+                const bool ok = (pa.x >> 16) == rtag && (pa.y >> 16) == rtag && (pa.z >> 16) == rtag && (pa.w >> 16) == rtag &&
+                                (pb.x >> 16) == rtag && (pb.y >> 16) == rtag && (pb.z >> 16) == rtag && (pb.w >> 16) == rtag;
+                if (ok) break;
+                if (clock64() - t0 > 4000000000LL) {  // a peer died: raise the error word and carry on with what is there (no hang, no trap)
+                  *reinterpret_cast<volatile uint32_t*>(p.ws) = 2u;
+                  break;
+                }
+              }
+              acc8[0] += bf16lo(pa.x); acc8[1] += bf16lo(pa.y); acc8[2] += bf16lo(pa.z); acc8[3] += bf16lo(pa.w);
+              acc8[4] += bf16lo(pb.x); acc8[5] += bf16lo(pb.y); acc8[6] += bf16lo(pb.z); acc8[7] += bf16lo(pb.w);
+            }
+            dv = make_uint4(pack_bf16(acc8[0], acc8[1]), pack_bf16(acc8[2], acc8[3]), pack_bf16(acc8[4], acc8[5]), pack_bf16(acc8[6], acc8[7]));
+          } else {
+            dv = *reinterpret_cast<const uint4*>(p.delta + (int64_t)b * p.K + c * 8);
+          }
+          v.x = pack_bf16(bf16lo(v.x) + bf16lo(dv.x), bf16hi(v.x) + bf16hi(dv.x));
+          v.y = pack_bf16(bf16lo(v.y) + bf16lo(dv.y), bf16hi(v.y) + bf16hi(dv.y));
+          v.z = pack_bf16(bf16lo(v.z) + bf16lo(dv.z), bf16hi(v.z) + bf16hi(dv.z));
+          v.w = pack_bf16(bf16lo(v.w) + bf16lo(dv.w), bf16hi(v.w) + bf16hi(dv.w));
+          if (p.x_out && designated) *reinterpret_cast<uint4*>(p.x_out + (int64_t)b * p.K + c * 8) = v;
+        }
+        *reinterpret_cast<uint4*>(sb + xs_chunk(b, c)) = v;
+        const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+  #pragma unroll
+        for (int i = 0; i < 4; ++i) { const float a = bf16lo(w4[i]), c2 = bf16hi(w4[i]); ss = fmaf(a, a, ss); ss = fmaf(c2, c2, ss); }
+      }
+      if (p.norm_w) {
+        ss = warp_sum(ss);
+        if (lane == 0) s_ssq[warp * 16 + b] = ss;
+      }
+    }
+    if (tid == 0 && p.debug == 3) v4_stamp_cyc(p, 3, c_rel);
+    if (p.norm_w) {
+      asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
+      if (tid == 0 && p.debug == 3) v4_stamp_cyc(p, 6, c_rel);
+      if (tid < B) {
+        float tot = 0.f;
+  #pragma unroll
+        for (int w = 0; w < kV4CW; ++w) tot += s_ssq[w * 16 + tid];
+        s_rstd[tid] = rsqrtf(tot / (float)p.K + p.eps);
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
+      for (int b = 0; b < B; ++b) {
+        const float rstd = s_rstd[b];
+        int ci = 0;
+        for (int c = tid; c < chunks; c += kV4Consumers, ++ci) {  // same thread owns the same chunk as above
+          uint4* px = reinterpret_cast<uint4*>(sb + xs_chunk(b, c));
+          uint4 v = *px;
+          const uint4 nw = ci == 0 ? nwreg[0] : ci == 1 ? nwreg[1] : ci == 2 ? nwreg[2] : *reinterpret_cast<const uint4*>(p.norm_w + c * 8);
+          // weight * (x * rstd), fp32, one cast (rmsnorm.py:24-25)
+          v.x = pack_bf16(bf16lo(nw.x) * (bf16lo(v.x) * rstd), bf16hi(nw.x) * (bf16hi(v.x) * rstd));
+          v.y = pack_bf16(bf16lo(nw.y) * (bf16lo(v.y) * rstd), bf16hi(nw.y) * (bf16hi(v.y) * rstd));
+          v.z = pack_bf16(bf16lo(nw.z) * (bf16lo(v.z) * rstd), bf16hi(nw.z) * (bf16hi(v.z) * rstd));
+          v.w = pack_bf16(bf16lo(nw.w) * (bf16lo(v.w) * rstd), bf16hi(nw.w) * (bf16hi(v.w) * rstd));
+          *px = v;
+        }
+      }
+      if (tid == 0 && p.debug == 3) v4_stamp_cyc(p, 7, c_rel);
     }
   }
   asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");  // activation rows and the table are published
+  if (tid == 0) v4_stamp(p, 2);
   if (p.tp_slots && tid == 0) {  // last CTA to have read the slots bumps the buffer's sequence counter for its next use
     const uint32_t old = atomicAdd(p.tp_recv_done, 1u);
     if (old == (uint32_t)G - 1u) {
@@ -477,7 +574,7 @@ __global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params 
   uint32_t xreg[XR][NB][8];
   float xsreg[XR];
   if constexpr (XREG) {
-    const int ku0 = (u0 + warp) % upt;   // the k-unit of every unit this warp will meet (unit stride == units per tile)
+    const int ku0 = ku_first;   // the k-unit of every unit this warp will meet (unit stride == units per tile)
 #pragma unroll
     for (int i = 0; i < XR; ++i) {
       load_x(xreg[i], ku0 * XR + i);
@@ -583,12 +680,13 @@ __global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params 
     ++jf; ++ct;
   };
 
-  int u = u0 + warp;
-  int tf = u / upt, ku = u - tf * upt;
+  int u = u_first;
+  int tf = tf_first, ku = ku_first;
   int s = 0;
   uint32_t ph = 0;
   for (; u < u1; u += kV4CW) {
     mbar_wait(full_a + s * 8, ph);
+    if (tid == 0 && u == u0) { if (p.debug == 3) v4_stamp_cyc(p, 4, c_rel); else v4_stamp(p, 3); }
     const uint32_t sp = stage_addr(s) + (uint32_t)warp * UB;
     uint4 w[RU][BPR];
     uint2 sc[RU];
@@ -616,11 +714,29 @@ __global__ void __launch_bounds__(kV4Threads, 1) qgemv_v4_kernel(const V4Params 
     if (++s == S) { s = 0; ph ^= 1u; }
   }
   while (ct <= t_last) flush();
+  if (tid == 0 && p.debug != 3) v4_stamp(p, 4);
 }
 
+static unsigned long long* g_v4_trace = nullptr;   // development: device buffer [slots][kV4MaxCtas][8]
+static int g_v4_trace_slots = 0, g_v4_trace_next = 0;
+void qgemv_v4_set_trace(void* buf, int slots) { g_v4_trace = reinterpret_cast<unsigned long long*>(buf); g_v4_trace_slots = slots; g_v4_trace_next = 0; }
+
+static std::atomic<int> g_v4_occ2{0};     // experiment: int4 batch-1 launches as two co-resident CTAs per SM
 static std::atomic<int> g_v4_split{-1};   // -1 auto, 0 never split entities, 1 always
 static std::atomic<int> g_v4_xreg{1};     // activation fragments in registers where the shape allows
 void qgemv_v4_tune(int split, int xreg) { g_v4_split = split; g_v4_xreg = xreg; }
+void qgemv_v4_tune_occ2(int on) { g_v4_occ2 = on; }
+
+template <int RU, bool INT4>
+static cudaError_t launch_v4_occ2(const V4Params& p, int gx, cudaStream_t st) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(qgemv_v4_kernel<RU, INT4, 0, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kV4DynSmem2);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  return launch(qgemv_v4_kernel<RU, INT4, 0, false, 2>, dim3(gx), dim3(kV4Threads), (size_t)kV4DynSmem2, st, p);
+}
 
 template <int RU, bool INT4, int MODE, bool XREG>
 static cudaError_t launch_v4(const V4Params& p, int gx, cudaStream_t st) {
@@ -637,6 +753,9 @@ template <bool INT4, int MODE>
 static cudaError_t launch_v4_ru(int ru, const V4Params& p, int gx, cudaStream_t st) {
   constexpr int RUMAX = INT4 ? 2 : 4;
   if (ru == RUMAX) {
+    if constexpr (MODE == 0 && INT4) {
+      if (g_v4_occ2.load()) return launch_v4_occ2<RUMAX, true>(p, gx, st);
+    }
     if constexpr (MODE == 0) {
       if (p.upt == kV4CW && g_v4_xreg.load()) return launch_v4<RUMAX, INT4, 0, true>(p, gx, st);
     }
@@ -666,7 +785,7 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a, int debug, cudaStream_t st) 
   for (int cand = int4 ? 2 : 4; cand >= 1; cand >>= 1) {
     if (nrec % cand) continue;
     const int stage = kV4CW * cand * (int4 ? 1088 : 576);
-    const V4Plan pl = v4_plan(1024u, stage, red_bytes, int4, a->batch, nkb, xstride, gap);
+    const V4Plan pl = v4_plan(1024u, stage, red_bytes, int4, a->batch, nkb, xstride, gap, (int4 && mode == 0 && g_v4_occ2.load()) ? kV4DynSmem2 : kV4DynSmem);
     if (pl.S >= 2) { ru = cand; break; }
   }
   if (ru == 0) return B200_ERR_UNSUPPORTED;
@@ -705,6 +824,7 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a, int debug, cudaStream_t st) 
       p.tp_recv_done = reinterpret_cast<uint32_t*>(h->recv_done);
     }
   }
+  if (g_v4_trace && g_v4_trace_next < g_v4_trace_slots) p.trace = g_v4_trace + (size_t)(g_v4_trace_next++) * kV4MaxCtas * 8;
   int gx = sm_count();
   if (gx > kV4MaxCtas) gx = kV4MaxCtas;
   // Whole entities per CTA unless the resulting imbalance costs more than the partial hand-off of a split entity

@@ -10,5 +10,8 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a, int debug, cudaStream_t st);
 size_t qgemv_v4_workspace_bytes();
 // development knobs.  split: -1 auto, 0 whole entities per CTA, 1 stream-K split; xreg: 0 = activations always from shared memory
 void qgemv_v4_tune(int split, int xreg);
+// development: per-CTA phase time stamps (globaltimer) of the next `slots` launches into buf[slots][160][8] (u64); NULL = off
+void qgemv_v4_set_trace(void* buf, int slots);
+void qgemv_v4_tune_occ2(int on);
 
 }  // namespace b200

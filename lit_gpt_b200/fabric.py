@@ -29,7 +29,12 @@ class Fabric:
         self.global_rank = int(os.environ.get("RANK", 0))
         self.world_size = int(os.environ.get("WORLD_SIZE", 1)) if strategy == "ddp" else 1
         use_cuda = torch.cuda.is_available() and accelerator in ("auto", "cuda", "gpu")
-        self.device = torch.device("cuda", self.local_rank if strategy == "ddp" else 0) if use_cuda else torch.device("cpu")
+        # B200_TP_SHARED_DEVICE=1: every rank drives cuda:0 and the control plane is gloo (two NCCL ranks cannot share a
+        # device).  The peer-memory hand-off works unchanged between processes on one GPU (CUDA IPC, time-sliced contexts);
+        # this is how the tensor-parallel decode path is tested on a one-GPU box (tests/test_gpu_tp_shared.py).
+        self.shared_device = strategy == "ddp" and os.environ.get("B200_TP_SHARED_DEVICE", "0") == "1"
+        index = self.local_rank if strategy == "ddp" and not self.shared_device else 0
+        self.device = torch.device("cuda", index) if use_cuda else torch.device("cpu")
         if self.device.type == "cuda":
             torch.cuda.set_device(self.device)
 
@@ -38,7 +43,7 @@ class Fabric:
         if self.world_size > 1 and not dist.is_initialized():
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
             os.environ.setdefault("MASTER_PORT", "29500")
-            backend = "nccl" if self.device.type == "cuda" else "gloo"
+            backend = "nccl" if self.device.type == "cuda" and not self.shared_device else "gloo"
             kw = {"device_id": self.device} if backend == "nccl" else {}
             dist.init_process_group(backend, rank=self.global_rank, world_size=self.world_size, **kw)
 
