@@ -35,7 +35,11 @@ WORKLOADS = {
     "mistral-7b-int4-bs1": ("Mistral-7B-v0.1", "int4", 1, 16, 0),
     "llama2-70b-int4-bs1-ctx2048": ("Llama-2-70b-hf", "int4", 1, 16, 2032),
 }
-BPP = {"nf4": 0.5 + 4 / 64, "fp4": 0.5 + 4 / 64, "int4": 0.5 + 4 / 128}  # bytes/param as the kernels read them
+# algorithmic bytes per parameter: nf4 / fp4 = 4 bits + one fp32 absmax per 64; int4 g128 = 4 bits + one fp16 scale and
+# one 4-bit zero-point per 128 (0.51953).  The kernels stream the fused half2 {scale, zero} form of int4 (0.53125): reported as
+# `streamed_bytes_per_param`, not used for the roofline fraction.
+BPP = {"nf4": 0.5 + 4 / 64, "fp4": 0.5 + 4 / 64, "int4": 0.5 + 2.5 / 128}
+BPP_STREAMED = {"nf4": 0.5 + 4 / 64, "fp4": 0.5 + 4 / 64, "int4": 0.5 + 4 / 128}
 
 
 def measured_peaks():
@@ -47,33 +51,63 @@ def measured_peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md clocks line)."""
+    """SM clock + throttle reasons sampled in-process through NVML every ~2 ms (B200_PROFILING.md clocks line); only the
+    samples taken between mark_start() and mark_end() -- the timed region -- are reported."""
 
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-
-    def __init__(self, index: int = 0):
+    def __init__(self, device: "torch.device"):
         super().__init__(daemon=True)
-        self.index, self.rows, self.proc = index, [], None
+        self.rows, self._stop_evt, self.t0, self.t1, self.handle, self.nv = [], threading.Event(), None, None, None, None
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(device).uuid)
+            try:
+                self.handle = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode())
+            except Exception:
+                self.handle = nv.nvmlDeviceGetHandleByIndex(device.index or 0)
+            self.nv = nv
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(self.handle, nv.NVML_CLOCK_SM))
+        except Exception as e:  # noqa: BLE001
+            self.err = str(e)
 
     def run(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
-                                          "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
-            for line in self.proc.stdout:
-                self.rows.append([c.strip() for c in line.split(",")])
-        except Exception:
-            pass
+        nv = self.nv
+        if nv is None:
+            return
+        while not self._stop_evt.is_set():
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)
+                try:
+                    reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+                except Exception:
+                    reasons = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                self.rows.append((time.perf_counter(), float(mhz), int(reasons)))
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def mark_start(self):
+        self.t0 = time.perf_counter()
+
+    def mark_end(self):
+        self.t1 = time.perf_counter()
 
     def stop(self) -> dict:
-        if self.proc is not None:
-            self.proc.terminate()
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(sm)}
+        self._stop_evt.set()
+        self.join(timeout=1.0)
+        nv = self.nv
+        if nv is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": "nvml unavailable: " + getattr(self, "err", "?")}
+        rows = [r for r in self.rows if self.t0 is not None and self.t0 <= r[0] <= (self.t1 or 1e99)]
+        bits = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4,
+                "hw_power_brake_slowdown": 0x80}
+        mask = 0
+        for r in rows:
+            mask |= r[2]
+        return {"sm_mhz": statistics.median([r[1] for r in rows]) if rows else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(n for n, b in bits.items() if mask & b), "samples": len(rows),
+                "source": "NVML in-process, 2 ms period, samples inside the timed region only"}
 
 
 def build_random_model(cfg_name: str, mode: str, max_seq: int, batch: int, fabric, n_layer=None):
@@ -174,7 +208,7 @@ def time_graph(graph, n: int, world: int) -> float:
     return float(ms.item())
 
 
-def cpu_reference_sample(cfg_name: str, steps: int, layers: int = 4) -> dict:
+def cpu_reference_sample(cfg_name: str, steps: int, layers: int = 4, warmup: int = 0) -> dict:
     """The reference's CPU path (generate/base.py on the host cores, fp32) restated by oracle/model_ref.py, on a
     BOUNDED sample: `layers` of the model's blocks at full width + the full lm_head, extrapolated to full depth."""
     from lit_gpt_b200 import Config
@@ -197,7 +231,7 @@ def cpu_reference_sample(cfg_name: str, steps: int, layers: int = 4) -> dict:
     p["transformer.wte.weight"] = torch.empty(cfg.padded_vocab_size, cfg.n_embd).normal_(0, 0.02, generator=g)
     p["lm_head.weight"] = torch.empty(cfg.padded_vocab_size, cfg.n_embd).normal_(0, 0.02, generator=g)
     T = 16
-    st = M.RefState(rc, T + steps + 2, 1, torch.float32, pos_dtype=torch.float32)
+    st = M.RefState(rc, T + steps + warmup + 2, 1, torch.float32, pos_dtype=torch.float32)
     prompt = torch.randint(0, cfg.vocab_size, (T,), generator=g)
     with torch.inference_mode():
         logits = M.gpt_forward(rc, p, prompt.view(1, -1), torch.arange(T), st)
@@ -208,16 +242,23 @@ def cpu_reference_sample(cfg_name: str, steps: int, layers: int = 4) -> dict:
         for _ in range(2):
             M.linear(M.rmsnorm(x, p["transformer.ln_f.weight"], cfg.norm_eps), p["lm_head.weight"])
         t_head = (time.perf_counter() - t0) / 2
-        t0 = time.perf_counter()
-        for i in range(steps):
+        for i in range(warmup):
             logits = M.gpt_forward(rc, p, tok.view(1, 1), torch.tensor([T + i]), st)
             tok = M.sample(logits, 0.0)
+        t0 = time.perf_counter()
+        for i in range(steps):
+            logits = M.gpt_forward(rc, p, tok.view(1, 1), torch.tensor([T + warmup + i]), st)
+            tok = M.sample(logits, 0.0)
         t_step = (time.perf_counter() - t0) / steps
-    t_full = (t_step - t_head) * cfg.n_layer / layers + t_head
-    return {"value": 1.0 / t_full, "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"oracle/model_ref.py generate loop (reference generate/base.py restated), fp32, {layers} of {cfg.n_layer} "
-                      f"blocks at full width + full lm_head, {steps} decode tokens after a {T}-token prompt; "
-                      f"measured {t_step * 1e3:.1f} ms/token on the sample, extrapolated to full depth ({t_full * 1e3:.1f} ms/token)"}
+    full = layers >= cfg.n_layer
+    t_full = t_step if full else (t_step - t_head) * cfg.n_layer / layers + t_head
+    depth = "all blocks (full depth, nothing extrapolated)" if full else \
+        f"{layers} of {cfg.n_layer} blocks at full width + full lm_head, extrapolated to full depth ({t_full * 1e3:.1f} ms/token)"
+    return {"value": 1.0 / t_full, "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port", "steps_timed": steps,
+            "timed_s": t_step * steps,
+            "sample": f"oracle/model_ref.py generate loop (reference generate/base.py restated), fp32, {depth}; "
+                      f"{steps} decode tokens timed after a {T}-token prompt and {warmup} warm-up tokens; "
+                      f"measured {t_step * 1e3:.1f} ms/token"}
 
 
 def run_reference(args) -> None:
@@ -225,14 +266,27 @@ def run_reference(args) -> None:
     if rank != 0:
         return
     cfg_name, mode, batch, T, ctx = WORKLOADS[args.workload]
-    steps = max(1, min(args.steps, 8))
+    from lit_gpt_b200 import Config
+
+    # exactly `--steps` decode tokens are timed after `--warmup` untimed ones.  Full depth when the host has the memory for
+    # the fp32 weights (7B: 27 GB) and the run stays within minutes; else a 4-block sample at full width, extrapolated
+    # (stated in cpu_baseline.sample either way).
+    cfg = Config.from_name(cfg_name)
+    per_layer = cfg.n_embd * (cfg.n_head + 2 * cfg.n_query_groups) * cfg.head_size + cfg.n_embd * cfg.n_embd + 3 * cfg.n_embd * cfg.intermediate_size
+    need = 4 * (cfg.n_layer * per_layer + 2 * cfg.padded_vocab_size * cfg.n_embd)
+    try:
+        import psutil
+
+        avail = psutil.virtual_memory().available
+    except Exception:
+        avail = 0
+    full_depth = avail > need * 1.3 and args.steps + args.warmup <= 64 and os.environ.get("B200_REF_SAMPLE", "0") != "1"
+    steps = max(1, args.steps)
     t0 = time.perf_counter()
-    for _ in range(min(args.warmup, 1)):
-        cpu_reference_sample(cfg_name, 1, layers=1)
-    cb = cpu_reference_sample(cfg_name, steps)
+    cb = cpu_reference_sample(cfg_name, steps, layers=cfg.n_layer if full_depth else 4, warmup=max(0, args.warmup))
     line = {
         "impl": "reference", "metric": "Llama-2-7B nf4 decode tok/s (bs=1)", "value": cb["value"], "unit": "tokens/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / cb["value"],
+        "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": 1e3 / cb["value"],
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "note": "reference CPU path (bitsandbytes has no CPU nf4: fp32 weights)"},
         "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -293,11 +347,13 @@ def run_ours(args) -> None:
     launches_per_step = K.launch_count() - n0
     dg.pos.fill_(ctx + T)
     dg.capture()
-    time_graph(dg.graph, W, world)
-    sampler = ClockSampler(dev.index or 0)
+    sampler = ClockSampler(dev)
     if rank == 0:
-        sampler.start()
+        sampler.start()   # running through the warm-up so that the first timed step is already covered
+    time_graph(dg.graph, W, world)
+    sampler.mark_start()
     ms = time_graph(dg.graph, K_steps, world)
+    sampler.mark_end()
     clocks = sampler.stop() if rank == 0 else {}
     tok_s = batch * K_steps / (ms / 1e3)
     ctx_mid = ctx + T + W + K_steps // 2
@@ -320,13 +376,18 @@ def run_ours(args) -> None:
     # dram__bytes_read + dram__bytes_write per launch from the committed ncu capture of this workload (ratio to the
     # algorithmic bytes, measured per layer shape); null for workloads that were not captured
     traffic = None
-    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r02_traffic.json")
+    if not os.path.exists(tpath):
+        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")
     if os.path.exists(tpath):
         tj = json.load(open(tpath))
         if tj.get("workload") == args.workload and world == 1:
             traffic = tj["traffic_over_algorithmic"] * bytes_step["weights"] / max(1, gemv_launches)
-    roofline = {"bound": "hbm", "kernel": "qgemv_stream_kernel", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
+    roofline = {"bound": "hbm", "kernel": "qgemv_v4_kernel", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": achieved / peaks["hbm_gbs"], "traffic": traffic,
+                "traffic_source": None if traffic is None else "constant: ncu dram__bytes_read+write of the committed capture (profiles/), "
+                                                                "scaled by this run's algorithmic bytes; not measured by this run",
+                "peak_source": peak_src, "streamed_bytes_per_param": BPP_STREAMED[mode],
                 "launches_per_step": gemv_launches, "avg_launch_us": gemv_ms * 1e3 / max(1, gemv_launches),
                 "algorithmic_bytes_per_launch": bytes_step["weights"] / max(1, gemv_launches),
                 "whole_step_frac": bytes_step["total"] / (ms / K_steps / 1e3) / 1e9 / peaks["hbm_gbs"],
@@ -401,15 +462,44 @@ def main() -> None:
     import torch.distributed as dist
 
     if dist.is_available() and dist.is_initialized():
-        # CUDA graphs that captured NCCL all-reduces keep the communicator busy at teardown (destroy_process_group and
-        # interpreter exit both hang): everything is printed and flushed, so leave without running destructors.
-        import torch
+        teardown()
 
-        torch.cuda.synchronize()
-        dist.barrier()
-        sys.stdout.flush()
+
+def teardown() -> None:
+    """Orderly multi-rank exit: captured graphs and peer mappings are dropped BEFORE the process group (a CUDA graph that
+    captured an NCCL collective keeps the communicator busy: destroying the group first is what used to hang).  A watchdog
+    turns a teardown that still does not finish within 30 s into a plain exit, after everything has been printed."""
+    import gc
+
+    import torch.distributed as dist
+
+    sys.stdout.flush()
+    sys.stderr.flush()
+
+    def _bail():
+        sys.stderr.write("bench.py: teardown did not finish within 30 s; leaving without destructors\n")
         sys.stderr.flush()
         os._exit(0)
+
+    wd = threading.Timer(30.0, _bail)
+    wd.daemon = True
+    wd.start()
+    torch.cuda.synchronize()
+    dist.barrier()
+    for obj in gc.get_objects():
+        try:
+            if type(obj).__name__ == "GPT" and hasattr(obj, "__dict__"):
+                obj.__dict__.pop("_decode_graphs", None)
+                comm = obj.__dict__.pop("_p2p", None)
+                if comm:
+                    comm.close()
+        except Exception:
+            pass
+    gc.collect()
+    torch.cuda.synchronize()
+    dist.barrier()
+    dist.destroy_process_group()
+    wd.cancel()
 
 
 if __name__ == "__main__":

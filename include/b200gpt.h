@@ -168,7 +168,19 @@ typedef struct b200_qgemv_tiled_args {
                               partial sums / arrival counters of row pairs cut by a stream-K boundary (self-cleaning) */
   size_t workspace_bytes;
   const struct b200_tp_handoff* tp; /* optional tensor-parallel hand-off (below); NULL on one GPU */
+  int fold;                /* 0 / 1: plain.  F = 2, 4: `tiled` holds the matrix VIEWED as (N / F, F * K), i.e. b200_tile_4bit(N / F, F * K)
+                              of the same flat nf4 / fp4 buffers: for row-parallel shards whose K is not a multiple of the
+                              64-element block while F * K is (generate/tp.py:28-45 cuts mlp.proj to 11008 / 8 = 1376 columns, and
+                              bitsandbytes quantizes the shard's FLAT storage, so blocks straddle rows).  N, K, x and y keep the
+                              true shapes; STORE / RESIDUAL epilogues, no norm / delta / tp consumer, batch * F <= 16. */
 } b200_qgemv_tiled_args;
+/* 1 when b200_qgemv_tiled would run these arguments on a streaming kernel, 0 when the shape is outside every plan (nothing
+ * is launched, pointers are not dereferenced): lets the caller choose the generic b200_qgemv / b200_qgemm up front. */
+int b200_qgemv_tiled_supported(const b200_qgemv_tiled_args* args);
+/* Bounded waits instead of hangs or traps: a kernel that waited ~2 s for a partner (a tensor-parallel peer's packets, a
+ * stream-K partner CTA) sets word 0 of the workspace and carries on.  This call synchronizes `stream`, returns the word in
+ * *code (0 = none, 1 = stream-K partner, 2 = tensor-parallel peer) and clears it.  generate() checks it at its sync points. */
+int b200_qgemv_tiled_error(void* workspace, b200_stream_t stream, unsigned int* code);
 size_t b200_qgemv_tiled_workspace_bytes(void);
 int b200_qgemv_tiled(const b200_qgemv_tiled_args* args, b200_stream_t stream);
 /* tuning: depth in {0(auto),2,4,6} items loaded ahead per warp; ctas_per_sm in {0(auto),1,2}; l2_prefetch 0/1 */

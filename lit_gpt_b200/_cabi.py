@@ -48,7 +48,7 @@ class QGemvTiledArgs(ctypes.Structure):
         ("norm_eps", c_float), ("batch", c_int), ("epilogue", c_int),
         ("bias", c_void_p), ("bias2", c_void_p), ("residual", c_void_p), ("y", c_void_p),
         ("prefetch", c_void_p), ("prefetch_bytes", c_int64), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
-        ("tp", ctypes.POINTER(TpHandoff)),
+        ("tp", ctypes.POINTER(TpHandoff)), ("fold", c_int),
     ]
 
 
@@ -98,6 +98,8 @@ _SIGNATURES = {
     "b200_qgemv_tiled_workspace_bytes": (c_size_t, []),
     "b200_qgemv_tiled_tune": (c_int, [c_int, c_int, c_int]),
     "b200_qgemv_tiled_trace": (c_int, [c_void_p, c_int]),
+    "b200_qgemv_tiled_supported": (c_int, [ctypes.POINTER(QGemvTiledArgs)]),
+    "b200_qgemv_tiled_error": (c_int, [c_void_p, c_void_p, ctypes.POINTER(ctypes.c_uint)]),
     "b200_rmsnorm": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
     "b200_attn_decode_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_attn_decode": (c_int, [ctypes.POINTER(AttnDecodeArgs), c_void_p]),

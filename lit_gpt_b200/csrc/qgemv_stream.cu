@@ -51,6 +51,7 @@ struct StreamParams {
   int tp_world;
   uint32_t* tp_peer_y[8];        // producer: this rank's slot on every rank
   const uint32_t* tp_send_seq;   // producer: local sequence counter of the buffer written
+  uint32_t* err;             // error word (workspace[0]): 2 = a tensor-parallel peer did not deliver within ~2 s
   const uint32_t* tp_slots;      // consumer: local slots (rank r at + r * tp_slot_stride packets)
   int64_t tp_slot_stride;
   uint32_t* tp_recv_seq;         // consumer: local sequence counter of the buffer read
@@ -263,7 +264,10 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
               const bool ok = (pa.x >> 16) == rtag && (pa.y >> 16) == rtag && (pa.z >> 16) == rtag && (pa.w >> 16) == rtag &&
                               (pb.x >> 16) == rtag && (pb.y >> 16) == rtag && (pb.z >> 16) == rtag && (pb.w >> 16) == rtag;
               if (ok) break;
-              if (clock64() - t0 > 8000000000LL) __trap();  // a peer died: fail loudly instead of hanging the GPU
+              if (clock64() - t0 > 4000000000LL) {  // a peer died: raise the error word (host: b200_qgemv_tiled_error) and go on; no hang, no trap
+                if (p.err) *reinterpret_cast<volatile uint32_t*>(p.err) = 2u;
+                break;
+              }
             }
             acc8[0] += bf16lo(pa.x); acc8[1] += bf16lo(pa.y); acc8[2] += bf16lo(pa.z); acc8[3] += bf16lo(pa.w);
             acc8[4] += bf16lo(pb.x); acc8[5] += bf16lo(pb.y); acc8[6] += bf16lo(pb.z); acc8[7] += bf16lo(pb.w);
@@ -588,9 +592,10 @@ int b200_qgemv_tiled_trace(void* buf, int slots) {
   return B200_OK;
 }
 
-int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
+// dry = true: validate the shape against the kernels' plans only (no pointer checks, no launch)
+static int qgemv_tiled_impl(const b200_qgemv_tiled_args* a, b200_stream_t stream, bool dry) {
   B200_CHECK_ARG(a != nullptr, "b200_qgemv_tiled: null args");
-  B200_CHECK_ARG(a->tiled && a->x && (a->y || (a->tp && a->tp->send_seq)), "b200_qgemv_tiled: null tiled/x/y pointer");
+  B200_CHECK_ARG(dry || (a->tiled && a->x && (a->y || (a->tp && a->tp->send_seq))), "b200_qgemv_tiled: null tiled/x/y pointer");
   B200_CHECK_ARG(a->N > 0 && a->K > 0, "b200_qgemv_tiled: N and K must be positive (N=%lld K=%lld)", (long long)a->N, (long long)a->K);
   B200_CHECK_ARG(a->batch >= 1 && a->batch <= 16, "b200_qgemv_tiled: batch must be in [1,16] (got %d); use b200_qgemm for prefill", a->batch);
   B200_CHECK_ARG(a->qtype == B200_Q_NF4 || a->qtype == B200_Q_FP4 || a->qtype == B200_Q_INT4, "b200_qgemv_tiled: bad qtype %d", a->qtype);
@@ -599,7 +604,15 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   B200_CHECK_ARG(a->epilogue != B200_EPI_RESIDUAL || a->residual, "b200_qgemv_tiled: RESIDUAL epilogue needs residual");
   B200_CHECK_ARG(a->x_out == nullptr || a->x_out != a->x, "b200_qgemv_tiled: x_out must not alias x");
   const bool int4 = a->qtype == B200_Q_INT4;
-  B200_CHECK_ARG(a->K % (int4 ? 128 : 64) == 0, "b200_qgemv_tiled: K must be a multiple of %d (got %lld)", int4 ? 128 : 64, (long long)a->K);
+  const int fold = a->fold > 1 ? a->fold : 1;
+  if (fold > 1) {
+    B200_CHECK_ARG((fold == 2 || fold == 4) && !int4 && a->N % fold == 0 && a->K % 8 == 0 && a->batch * fold <= 16,
+                   "b200_qgemv_tiled: fold %d needs nf4 / fp4, N %% fold == 0, K %% 8 == 0 and batch * fold <= 16", fold);
+    B200_CHECK_ARG(a->epilogue != B200_EPI_SWIGLU && !a->norm_weight && !a->delta && !a->x_out && !(a->tp && a->tp->slots),
+                   "b200_qgemv_tiled: a folded matrix supports the STORE / RESIDUAL epilogues only (no norm, delta, x_out, tp consumer)");
+  }
+  B200_CHECK_ARG((a->K * fold) % (int4 ? 128 : 64) == 0, "b200_qgemv_tiled: K%s must be a multiple of %d (got %lld)", fold > 1 ? " * fold" : "",
+                 int4 ? 128 : 64, (long long)a->K);
   B200_CHECK_ARG(((reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(a->tiled) | reinterpret_cast<uintptr_t>(a->tiled2) |
                    reinterpret_cast<uintptr_t>(a->delta) | reinterpret_cast<uintptr_t>(a->x_out) |
                    reinterpret_cast<uintptr_t>(a->norm_weight) | reinterpret_cast<uintptr_t>(a->prefetch)) & 15) == 0,
@@ -620,8 +633,12 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   }
   // stream-K kernel (qgemv_v4.cu) unless forced off (tune depth 98) or the shape is outside its plan
   if (g_stream_depth.load() != 98) {
-    const int rc = qgemv_v4_launch(a, g_stream_depth.load() == 99 ? 1 : g_stream_depth.load() == 97 ? 3 : 0, (cudaStream_t)stream);  // 99: stream only, 97: prologue cycle stamps
+    const int rc = qgemv_v4_launch(a, g_stream_depth.load() == 99 ? 1 : g_stream_depth.load() == 97 ? 3 : 0, (cudaStream_t)stream, dry);  // 99: stream only, 97: prologue cycle stamps
     if (rc != B200_ERR_UNSUPPORTED) return rc;
+  }
+  if (fold > 1) {
+    set_error("b200_qgemv_tiled: batch %d x K %lld (fold %d) does not fit the stream-K kernel's shared memory plan", a->batch, (long long)a->K, fold);
+    return B200_ERR_UNSUPPORTED;
   }
 
   StreamParams p{};
@@ -642,6 +659,7 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   p.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual);
   p.y = reinterpret_cast<__nv_bfloat16*>(a->y);
   p.xstride = (int)a->K + 8;
+  p.err = (a->workspace && a->workspace_bytes >= 4) ? reinterpret_cast<uint32_t*>(a->workspace) : nullptr;
   p.debug = g_stream_depth.load() == 99 ? 1 : 0;
   if (g_stream_pf.load() && a->prefetch && a->prefetch_bytes >= 16) { p.pf = reinterpret_cast<const uint8_t*>(a->prefetch); p.pf_bytes = a->prefetch_bytes; }
 
@@ -690,6 +708,7 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
               a->batch, (long long)a->K, (size_t)a->batch * p.xstride * 2);
     return B200_ERR_UNSUPPORTED;
   }
+  if (dry) return B200_OK;
   const int steps = swiglu ? p.nunits : (p.nunits + 1) / 2;
   int gx = sm_count();
   if (gx > steps) gx = steps;
@@ -703,5 +722,17 @@ int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) {
   }
   return B200_OK;
 }
+
+int b200_qgemv_tiled(const b200_qgemv_tiled_args* a, b200_stream_t stream) { return qgemv_tiled_impl(a, stream, false); }
+
+int b200_qgemv_tiled_error(void* workspace, b200_stream_t stream, unsigned int* code) {
+  B200_CHECK_ARG(workspace && code, "b200_qgemv_tiled_error: null argument");
+  B200_CUDA(cudaMemcpyAsync(code, workspace, 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  B200_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  if (*code) B200_CUDA(cudaMemsetAsync(workspace, 0, 4, (cudaStream_t)stream));
+  return B200_OK;
+}
+
+int b200_qgemv_tiled_supported(const b200_qgemv_tiled_args* a) { return qgemv_tiled_impl(a, nullptr, true) == B200_OK ? 1 : 0; }
 
 }  // extern "C"

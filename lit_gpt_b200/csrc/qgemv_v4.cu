@@ -69,6 +69,9 @@ struct V4Params {
   int64_t tp_slot_stride;
   uint32_t* tp_recv_seq;
   uint32_t* tp_recv_done;
+  int fold;         // row folding (b200_qgemv_tiled_args::fold): N, K, batch above are the FOLDED view; outputs are unfolded
+  int64_t Nout;     // true output features (fold * N)
+  int Kin;          // true input features (K / fold)
   unsigned long long* trace;   // development: [cta][8] globaltimer stamps of this launch (NULL = off)
 };
 
@@ -217,14 +220,18 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
     uint32_t* wsflag = reinterpret_cast<uint32_t*>(p.ws + 64);
     const uint32_t stag = p.tp_send_seq ? (__ldcg(p.tp_send_seq) % 65535u) + 1u : 0u;
     auto store_out = [&](int64_t n, int c, float v) {  // STORE / RESIDUAL epilogues for one (row, batch column)
+      if (p.fold > 1) {  // folded view: row n holds the true rows n * fold + h, column c = batch row * fold + h
+        n = n * p.fold + (c % p.fold);
+        c /= p.fold;
+      }
       float h = v + (p.bias ? __bfloat162float(p.bias[n]) : 0.f);
-      if (p.epilogue == B200_EPI_RESIDUAL) h = round_bf16(h) + __bfloat162float(p.residual[(int64_t)c * p.N + n]);
+      if (p.epilogue == B200_EPI_RESIDUAL) h = round_bf16(h) + __bfloat162float(p.residual[(int64_t)c * p.Nout + n]);
       const __nv_bfloat16 hb = __float2bfloat16_rn(h);
-      if (p.y) p.y[(int64_t)c * p.N + n] = hb;
+      if (p.y) p.y[(int64_t)c * p.Nout + n] = hb;
       if (p.tp_send_seq) {  // row-parallel partial: one self-validating packet straight into every rank's slot over NVLink
         const uint32_t pk = (stag << 16) | (uint32_t)bf16_bits(h);
         for (int r = 0; r < p.tp_world; ++r)
-          asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p.tp_peer_y[r] + (int64_t)c * p.N + n), "r"(pk) : "memory");
+          asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p.tp_peer_y[r] + (int64_t)c * p.Nout + n), "r"(pk) : "memory");
       }
     };
     const int e_first = t_first / TS, e_last = t_last / TS;
@@ -449,7 +456,13 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
     for (int b = 0; b < B; ++b) {
       float ss = 0.f;
       for (int c = tid; c < chunks; c += kV4Consumers) {
-        uint4 v = *reinterpret_cast<const uint4*>(p.x + (int64_t)b * p.K + c * 8);
+        uint4 v;
+        if (p.fold > 1) {  // folded row b = (true row b / fold, segment h): the activation in segment h, zeros elsewhere
+          const int h = b % p.fold, e0 = c * 8 - h * p.Kin;
+          v = (e0 >= 0 && e0 < p.Kin) ? *reinterpret_cast<const uint4*>(p.x + (int64_t)(b / p.fold) * p.Kin + e0) : make_uint4(0u, 0u, 0u, 0u);
+        } else {
+          v = *reinterpret_cast<const uint4*>(p.x + (int64_t)b * p.K + c * 8);
+        }
         if (p.delta || p.tp_slots) {
           uint4 dv;
           if (p.tp_slots) {  // sum of the ranks' partials in rank order (fp32), rounded once to bf16 like an all-reduced tensor
@@ -769,7 +782,12 @@ static cudaError_t launch_v4_ru(int ru, const V4Params& p, int gx, cudaStream_t 
 
 size_t qgemv_v4_workspace_bytes() { return kV4WsData + (size_t)kV4MaxCtas * kV4WsPerCta; }
 
-int qgemv_v4_launch(const b200_qgemv_tiled_args* a, int debug, cudaStream_t st) {
+int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st, bool dry) {
+  // row folding: run the kernel on the (N / F, F * K) view with F activation rows per true row (zero outside their segment)
+  const int fold = a0->fold > 1 ? a0->fold : 1;
+  b200_qgemv_tiled_args av = *a0;
+  av.N = a0->N / fold; av.K = a0->K * fold; av.batch = a0->batch * fold;
+  const b200_qgemv_tiled_args* a = &av;
   const bool int4 = a->qtype == B200_Q_INT4;
   const bool swiglu = a->epilogue == B200_EPI_SWIGLU;
   const int nkb = (int)(a->K / 64);
@@ -779,7 +797,7 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a, int debug, cudaStream_t st) 
   const int red_bytes = (mode == 0 ? 4 * kV4CW * 16 : 2 * kV4CW * 16 * cols) * 4;
   const int xstride = (int)a->K + 8;
   const int gap = (!int4 && mode == 0 && nkb <= 256) ? 1 : 0;
-  if (a->workspace == nullptr || a->workspace_bytes < qgemv_v4_workspace_bytes()) return B200_ERR_UNSUPPORTED;
+  if (!dry && (a->workspace == nullptr || a->workspace_bytes < qgemv_v4_workspace_bytes())) return B200_ERR_UNSUPPORTED;
   // largest unit (records per unit) that divides the tile and leaves at least two ring stages
   int ru = 0;
   for (int cand = int4 ? 2 : 4; cand >= 1; cand >>= 1) {
@@ -793,6 +811,7 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a, int debug, cudaStream_t st) 
   const int ts = swiglu ? 2 : 1;
   const int64_t U = ntiles * ts * (nrec / ru);
   if (U <= 0 || U > 0x3fffffff) return B200_ERR_UNSUPPORTED;
+  if (dry) return B200_OK;
 
   V4Params p{};
   p.tA = reinterpret_cast<const uint8_t*>(a->tiled);
@@ -809,6 +828,7 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a, int debug, cudaStream_t st) 
   p.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual);
   p.y = reinterpret_cast<__nv_bfloat16*>(a->y);
   p.xstride = xstride; p.gap = gap;
+  p.fold = fold; p.Nout = a0->N; p.Kin = (int)a0->K;
   p.ws = reinterpret_cast<uint8_t*>(a->workspace);
   if (a->tp) {
     const b200_tp_handoff* h = a->tp;

@@ -6,7 +6,7 @@ namespace b200 {
 
 // returns B200_OK, an error (message set), or B200_ERR_UNSUPPORTED *without* a message when the shape is outside
 // what this kernel covers (the caller then uses the older row-tile kernel)
-int qgemv_v4_launch(const b200_qgemv_tiled_args* a, int debug, cudaStream_t st);
+int qgemv_v4_launch(const b200_qgemv_tiled_args* a, int debug, cudaStream_t st, bool dry = false);  // dry: plan check only
 size_t qgemv_v4_workspace_bytes();
 // development knobs.  split: -1 auto, 0 whole entities per CTA, 1 stream-K split; xreg: 0 = activations always from shared memory
 void qgemv_v4_tune(int split, int xreg);

@@ -159,6 +159,8 @@ def generate(model: GPT, prompt: torch.Tensor, max_returned_tokens: int, *, temp
                     break
         if n_valid:
             tokens.append(dg.history[T + 1 : T + 1 + min(n_valid, done)].clone())
+        if getattr(model, "tp_world_size", 1) > 1:  # a peer that died mid-sequence shows up here, not as a hung GPU
+            K.check_gemv_errors(device)
         return torch.cat(tokens)
 
     for _ in range(2, max_returned_tokens - T + 1):

@@ -6,9 +6,11 @@ graph.  CUDA tensors only — no CPU path exists (``B200Error`` is raised instea
 from __future__ import annotations
 
 import ctypes
+import functools
 from typing import Dict, Optional, Tuple
 
 import torch
+import torch._dynamo
 
 from . import _cabi as C
 
@@ -271,9 +273,10 @@ def qgemv_tiled(x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, quant_type
                 x_out: Optional[torch.Tensor] = None, norm_weight: Optional[torch.Tensor] = None, norm_eps: float = 1e-5,
                 residual: Optional[torch.Tensor] = None, tiled2: Optional[torch.Tensor] = None,
                 prefetch: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-                tp: Optional["C.TpHandoff"] = None) -> torch.Tensor:
+                tp: Optional["C.TpHandoff"] = None, fold: int = 1) -> torch.Tensor:
     """y = epilogue(prologue(x) @ dequant(W).T) over tiled matrices; see b200_qgemv_tiled in include/b200gpt.h.
-    ``tp``: tensor-parallel hand-off over peer memory (lit_gpt_b200/p2p.py builds it)."""
+    ``tp``: tensor-parallel hand-off over peer memory (lit_gpt_b200/p2p.py builds it).  ``fold``: the tiled buffer is
+    the (N / fold, fold * K) view of the flat 4-bit storage (shards whose K is not a multiple of the block)."""
     C.require_cuda(x, tiled)
     x = _bf16c(x, "x")
     if x.shape[-1] != K:
@@ -290,9 +293,41 @@ def qgemv_tiled(x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, quant_type
         delta=C.ptr(delta), x_out=C.ptr(x_out), norm_weight=C.ptr(norm_weight), norm_eps=norm_eps, batch=batch, epilogue=epilogue,
         bias=C.ptr(bias), bias2=C.ptr(bias2), residual=C.ptr(residual), y=y.data_ptr(), prefetch=C.ptr(prefetch),
         prefetch_bytes=0 if prefetch is None else prefetch.numel() * prefetch.element_size(),
-        workspace=ws.data_ptr(), workspace_bytes=ws.numel(), tp=None if tp is None else ctypes.pointer(tp))
+        workspace=ws.data_ptr(), workspace_bytes=ws.numel(), tp=None if tp is None else ctypes.pointer(tp), fold=fold)
     C.check(C.load().b200_qgemv_tiled(ctypes.byref(args), C.stream_ptr(x.device)), "qgemv_tiled")
     return y
+
+
+@functools.lru_cache(maxsize=None)
+def _qgemv_tiled_supported(N: int, K: int, quant_type: str, batch: int, swiglu: bool, fold: int) -> bool:
+    args = C.QGemvTiledArgs(qtype=QTYPES[quant_type], blocksize=128 if quant_type == "int4" else 64, N=N, K=K, batch=batch,
+                            epilogue=C.EPI_SWIGLU if swiglu else C.EPI_STORE, tiled2=256 if swiglu else None, fold=fold)  # dry run: pointers are not dereferenced
+    return bool(C.load().b200_qgemv_tiled_supported(ctypes.byref(args)))
+
+
+@torch._dynamo.assume_constant_result
+def qgemv_tiled_supported(N: int, K: int, quant_type: str, batch: int, swiglu: bool = False, fold: int = 1) -> bool:
+    """Whether b200_qgemv_tiled runs (batch, K) x (N, K) on a streaming kernel (its shared-memory plan covers the
+    activation rows); asked up front so that the caller can pick the generic GEMV / the prefill GEMM instead.
+    A pure function of the shape: a constant while tracing (no graph break)."""
+    if not 1 <= batch <= 16:
+        return False
+    return _qgemv_tiled_supported(int(N), int(K), quant_type, int(batch), bool(swiglu), int(fold))
+
+
+def check_gemv_errors(device: torch.device) -> None:
+    """Raise if a GEMV kernel on `device` gave up a bounded wait (a tensor-parallel peer that never delivered its
+    packets, a stream-K partner CTA): synchronizes the current stream.  Called by generate() at its sync points."""
+    key = ("qgemv_tiled", device.index if device.index is not None else torch.cuda.current_device())
+    ws = _workspaces.get(key)
+    if ws is None:
+        return
+    code = ctypes.c_uint(0)
+    with torch.cuda.device(device):
+        C.check(C.load().b200_qgemv_tiled_error(ws.data_ptr(), C.stream_ptr(device), ctypes.byref(code)), "qgemv_tiled_error")
+    if code.value:
+        what = {1: "a stream-K partner CTA", 2: "a tensor-parallel peer"}.get(code.value, f"code {code.value}")
+        raise C.B200Error(f"dequant-GEMV: {what} did not deliver within the bounded wait; the output of this step is invalid")
 
 
 def qgemv_tiled_tune(depth: int = 0, ctas_per_sm: int = 0, l2_prefetch: bool = True) -> None:

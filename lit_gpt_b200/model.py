@@ -206,8 +206,7 @@ class GPT(nn.Module):
         # e.g. 11008 / 8): that hand-off alone then stays an NCCL all-reduce, the attention branch still uses peer memory
         lins = [self.lm_head] + [l for b in blocks for l in (b.attn.attn, b.attn.proj, b.mlp.fc_1, b.mlp.fc_2)]
         lins += [b.mlp.proj for b in blocks if b.mlp.proj.tiled is not None]
-        ok = (os.environ.get("B200_TP_NCCL", "0") != "1" and all(l.tiled is not None for l in lins)
-              and all(16 * (2 * l.in_features + 16) <= 48 * 1024 or batch * (2 * l.in_features + 16) <= 48 * 1024 for l in lins))
+        ok = os.environ.get("B200_TP_NCCL", "0") != "1" and all(l.streams(batch) for l in lins)
         comm: Any = False
         if ok:
             try:
@@ -244,7 +243,7 @@ class GPT(nn.Module):
             def tlin(q: QLinear, inp: torch.Tensor, other: Optional[QLinear] = None, send: Optional[int] = None,
                      recv: Optional[int] = None, **kw: Any) -> torch.Tensor:
                 return K.qgemv_tiled(inp, q.tiled, q.out_features, q.in_features, q.quant_type, q.blocksize,
-                                     tiled2=None if other is None else other.tiled, tp=comm.handoff(send, recv), **kw)
+                                     tiled2=None if other is None else other.tiled, tp=comm.handoff(send, recv), fold=q.fold, **kw)
 
             # pending: how the previous block's MLP output reaches the next prologue: "p2p" (slots of buffer 1), a tensor
             # (NCCL all-reduced delta; the collective also orders the ranks, so reusing buffer 0 next block stays race-free)

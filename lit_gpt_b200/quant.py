@@ -70,6 +70,9 @@ class QLinear(nn.Module):
         self.sz: Optional[torch.Tensor] = None
         # kernel-side tiled copy (csrc/tile.cu) consumed by the streaming GEMV; None when the shape is not covered
         self.tiled: Optional[torch.Tensor] = None
+        # row folding of the tiled copy: the flat storage viewed as (out / fold, fold * in) when in_features is not a multiple
+        # of the quantisation block (row-parallel shards such as 11008 / 8 = 1376, generate/tp.py:28-45)
+        self.fold = 1
 
     # -- construction from an existing nn.Linear (convert_module path, generate/tp.py:171) -------------------
     @classmethod
@@ -135,9 +138,23 @@ class QLinear(nn.Module):
             self.absmax = absmax
         if self.bias is not None and self.bias.dtype != self.compute_dtype:
             self.bias = nn.Parameter(self.bias.data.to(self.compute_dtype), requires_grad=False)
-        self.tiled = None
-        if K.tiled_bytes(shape[0], shape[1], self.quant_type):
-            self.tiled = K.tile_4bit(self.weight.data, self.scale, shape[0], shape[1], self.quant_type, self.blocksize)
+        self._build_tiled(shape)
+
+    def _build_tiled(self, shape) -> None:
+        """The kernel-side layout: a byte permutation of the packed weight (csrc/tile.cu).  bitsandbytes quantizes the FLAT
+        storage, so when in_features is not a multiple of the block the blocks straddle rows; the same flat buffers viewed
+        as (N / F, F * K) are block-aligned and tile normally, and the GEMV unfolds the outputs (b200_qgemv_tiled `fold`)."""
+        self.tiled, self.fold = None, 1
+        N, Kd = int(shape[0]), int(shape[1])
+        if K.tiled_bytes(N, Kd, self.quant_type):
+            self.tiled = K.tile_4bit(self.weight.data, self.scale, N, Kd, self.quant_type, self.blocksize)
+            return
+        if self.quant_type != "int4" and Kd % 8 == 0:
+            for f in (2, 4):
+                if N % f == 0 and K.tiled_bytes(N // f, Kd * f, self.quant_type):
+                    self.tiled = K.tile_4bit(self.weight.data, self.scale, N // f, Kd * f, self.quant_type, self.blocksize)
+                    self.fold = f
+                    return
 
     # -- pre-quantized checkpoints (SURVEY §8f-2): the packed tensors go to disk as they are, no re-quantisation on load --
     def export_packed(self) -> dict:
@@ -190,8 +207,8 @@ class QLinear(nn.Module):
             self.quant_state = [self.absmax, torch.Size(shape), self.compute_dtype, self.blocksize, None, self.quant_type, None]
         if "bias" in st and self.bias is not None:
             self.bias = nn.Parameter(st["bias"].to(dev), requires_grad=False)
-        if self.quant_type != "int8" and K.tiled_bytes(shape[0], shape[1], self.quant_type):
-            self.tiled = K.tile_4bit(self.weight.data, self.scale, shape[0], shape[1], self.quant_type, self.blocksize)
+        if self.quant_type != "int8":
+            self._build_tiled(shape)
 
     def dequantize(self, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
         """(out_features, in_features) tensor of code[c] * absmax — bit-exact to oracle/quant_ref.py."""
@@ -275,7 +292,7 @@ class QLinear(nn.Module):
         if torch.compiler.is_compiling():  # traced: one opaque b200gpt::qlinear* node (lit_gpt_b200/ops.py), no graph break
             from . import ops  # noqa: F401
 
-            if self.tiled is not None and rows * (2 * self.in_features + 16) <= 48 * 1024 and rows <= GEMV_MAX_ROWS:
+            if self.fold == 1 and self.streams(rows):
                 y = torch.ops.b200gpt.qlinear_tiled(x, self.tiled, self.out_features, self.in_features, self.quant_type, self.blocksize, self.bias)
             else:
                 y = torch.ops.b200gpt.qlinear(x, self.weight.data, self.scale, self.out_features, self.in_features, self.quant_type,
@@ -284,11 +301,17 @@ class QLinear(nn.Module):
         # <= 16 rows: the streaming GEMV, provided the activation rows fit its shared-memory plan (a 16-token prompt at
         # K = 8192 does not: that call is a small prefill and takes the GEMM); shapes without a tiled layout (toy
         # configs) keep the reference-layout GEMV
-        if rows <= GEMV_MAX_ROWS and (self.tiled is None or rows == 1 or rows * (2 * self.in_features + 16) <= 48 * 1024):
+        if rows <= GEMV_MAX_ROWS and (self.tiled is None or self.streams(rows)):
             y = self.gemv(x, bias=self.bias)
         else:
             y = prefill_linear(self, x)
         return y if in_dtype == torch.bfloat16 else y.to(in_dtype)
+
+    def streams(self, rows: int, swiglu: bool = False) -> bool:
+        """True when `rows` activation rows run on the streaming GEMV over the tiled layout (asked of the library: the
+        kernel's shared-memory plan must hold the activation rows)."""
+        return (self.tiled is not None and rows <= GEMV_MAX_ROWS
+                and K.qgemv_tiled_supported(self.out_features, self.in_features, self.quant_type, rows, swiglu, self.fold))
 
     def gemv(self, x: torch.Tensor, other: Optional["QLinear"] = None, prefetch: Optional[torch.Tensor] = None,
              **kw: Any) -> torch.Tensor:
@@ -298,12 +321,11 @@ class QLinear(nn.Module):
         if self.quant_type == "int8":
             raise B200Error("QLinear.gemv is the 4-bit fused path; int8 modules go through forward()")
         rows = x.numel() // self.in_features
-        if self.tiled is not None and (other is None or other.tiled is not None) and rows * (2 * self.in_features + 16) <= 48 * 1024:
-            try:
-                return K.qgemv_tiled(x, self.tiled, self.out_features, self.in_features, self.quant_type, self.blocksize,
-                                     tiled2=None if other is None else other.tiled, prefetch=prefetch, **kw)
-            except NotImplementedError:  # shape outside the streaming kernel's shared-memory plan: nothing was launched
-                pass
+        plain = not any(kw.get(k) is not None for k in ("norm_weight", "delta", "x_out", "bias", "bias2"))
+        if (other is None or (other.tiled is not None and other.fold == 1 and self.fold == 1)) and (self.fold == 1 or plain) \
+                and self.streams(rows, swiglu=other is not None):
+            return K.qgemv_tiled(x, self.tiled, self.out_features, self.in_features, self.quant_type, self.blocksize,
+                                 tiled2=None if other is None else other.tiled, prefetch=prefetch, fold=self.fold, **kw)
         if other is not None:
             kw.update(packed2=other.weight.data, scale2=other.scale)
         kw.pop("bias2", None)

@@ -219,7 +219,9 @@ def sample(logits: Tensor, temperature: float = 1.0, top_k: Optional[int] = None
 @torch.inference_mode()
 def generate(cfg: RefConfig, p: Dict[str, Tensor], state: RefState, prompt: Tensor, max_returned_tokens: int, *,
              temperature: float = 1.0, top_k: Optional[int] = None, eos_id: Optional[int] = None,
-             return_logits: bool = False):
+             return_logits: bool = False, forced: Optional[Tensor] = None):
+    """`forced` (test helper, no counterpart in the reference): a full token sequence to follow instead of sampling, so that
+    two precisions can be compared step by step along the SAME tokens (teacher forcing)."""
     T = prompt.size(0)
     assert max_returned_tokens > T
     if state.max_seq_length < max_returned_tokens - 1:
@@ -229,12 +231,12 @@ def generate(cfg: RefConfig, p: Dict[str, Tensor], state: RefState, prompt: Tens
     input_pos = torch.tensor([T])
     logits = gpt_forward(cfg, p, prompt.view(1, -1), torch.arange(0, T), state)
     all_logits.append(logits[0, -1].clone())
-    token = sample(logits, temperature, top_k).to(prompt.dtype)
+    token = sample(logits, temperature, top_k).to(prompt.dtype) if forced is None else forced[T].view(1).to(prompt.dtype)
     tokens.append(token)
-    for _ in range(2, max_returned_tokens - T + 1):
+    for i in range(2, max_returned_tokens - T + 1):
         logits = gpt_forward(cfg, p, token.view(1, -1), input_pos, state)
         all_logits.append(logits[0, -1].clone())
-        token = sample(logits, temperature, top_k).to(prompt.dtype)
+        token = sample(logits, temperature, top_k).to(prompt.dtype) if forced is None else forced[T + i - 1].view(1).to(prompt.dtype)
         tokens.append(token)
         if eos_id is not None and token == eos_id:
             break

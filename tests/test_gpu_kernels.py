@@ -125,6 +125,28 @@ def test_qgemv_tuning_variants_agree(K, ks, occ):
     _check_gemv(y, x.float(), deq)
 
 
+@pytest.mark.parametrize("qt", ["nf4", "fp4"])
+@pytest.mark.parametrize("N,Kdim,B,fold", [(4096, 1376, 1, 2), (256, 96, 3, 2), (512, 1376, 8, 2), (64, 48, 2, 4), (4096, 1376, 4, 2)])
+def test_qgemv_tiled_folded_rows(K, qt, N, Kdim, B, fold):
+    """A row-parallel shard whose K is not a multiple of the 64-element block (generate/tp.py:28-45: 11008 / 8 = 1376):
+    bitsandbytes quantizes the shard's FLAT storage, so blocks straddle rows.  The same flat buffers viewed as
+    (N / fold, fold * K) tile normally; the GEMV unfolds (b200_qgemv_tiled `fold`).  Checked against the oracle's
+    dequantised (N, K) matrix, plain and with the residual epilogue."""
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, B, qt, seed=N + B)
+    assert K.tiled_bytes(N, Kdim, qt) == 0
+    tiled = K.tile_4bit(packed, scale, N // fold, Kdim * fold, qt, bs)
+    assert K.qgemv_tiled_supported(N, Kdim, qt, B, False, fold)
+    y = K.qgemv_tiled(x.cuda(), tiled, N, Kdim, qt, bs, fold=fold)
+    assert y.shape == (B, N)
+    _check_gemv(y, x.float(), deq)
+    res = _randw((B, N), 7, std=1.0)
+    y2 = K.qgemv_tiled(x.cuda(), tiled, N, Kdim, qt, bs, fold=fold, residual=res.cuda())
+    _check_gemv(y2, x.float(), deq, post=lambda t: t.to(torch.bfloat16).float() + res.float())
+    # same numbers as the reference-layout kernel up to the order of the partial sums
+    y_ref = K.qgemv(x.cuda(), packed, scale, N, Kdim, qt, bs)
+    assert (y.float() - y_ref.float()).abs().max() <= 2 ** -6 * max(1e-3, y_ref.float().abs().max().item())
+
+
 @pytest.mark.parametrize("qt", ["nf4", "int4"])
 @pytest.mark.parametrize("N,Kdim,B", [(86, 32, 1), (33, 100, 2), (352, 96, 16), (7, 8, 1), (512, 1376, 1), (48, 1376, 5)])  # 1376 = 11008 / 8: TP-8 shard
 def test_qgemv_generic_path_odd_shapes(K, qt, N, Kdim, B):

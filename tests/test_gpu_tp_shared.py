@@ -13,10 +13,10 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
 
 
-def _run(world, mode, n_head, n_groups, seq0=0, port=29641):
+def _run(world, mode, n_head, n_groups, seq0=0, port=29641, inter=0):
     env = dict(os.environ, B200_TP_SHARED_DEVICE="1", B200_TP_NCCL="0", OMP_NUM_THREADS="4")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
-           "--master-port", str(port), os.path.join(ROOT, "tests", "tp_shared_worker.py"), ROOT, mode, str(n_head), str(n_groups), str(seq0)]
+           "--master-port", str(port), os.path.join(ROOT, "tests", "tp_shared_worker.py"), ROOT, mode, str(n_head), str(n_groups), str(seq0), str(inter)]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
     assert out.returncode == 0 and "TP_SHARED_OK" in out.stdout, out.stdout[-3000:] + out.stderr[-6000:]
     print(out.stdout[-600:])
@@ -35,3 +35,9 @@ def test_tp2_tag_wraparound():
 def test_tp4_per_rank_mqa_int4():
     # the Llama-2-70B pattern: n_query_groups == world, every rank is left with ONE kv group (MQA per rank)
     _run(4, "int4", 8, 4, port=29643)
+
+
+def test_tp8_row_shard_not_block_aligned():
+    # Llama-2-7B at world 8: mlp.proj is cut to 11008 / 8 = 1376 columns, not a multiple of the 64-element block -> the
+    # folded tiled layout (QLinear.fold == 2) keeps that Linear on the streaming kernel and on the peer-memory hand-off
+    _run(8, "nf4", 8, 8, port=29644, inter=11008)

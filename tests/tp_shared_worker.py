@@ -9,7 +9,7 @@ W' = concat_r dequant(quant(shard_r(W))) (oracle/quant_ref: rows for column-para
 Tolerance = the rule of tests/test_gpu_model.py: 2 x (error of the bf16 reference formulation) + 1e-3 * max|logit|;
 greedy tokens must agree on every step whose oracle top-1 / top-2 margin exceeds it.
 
-argv: repo_root mode n_head n_query_groups [seq0]
+argv: repo_root mode n_head n_query_groups [seq0 [intermediate_size]]
 """
 import os
 import sys
@@ -66,11 +66,12 @@ def raw_u32(ptr: int, n: int, device) -> torch.Tensor:
 def main() -> None:
     mode, n_head, n_groups = sys.argv[2], int(sys.argv[3]), int(sys.argv[4])
     seq0 = int(sys.argv[5]) if len(sys.argv) > 5 else 0
+    inter = int(sys.argv[6]) if len(sys.argv) > 6 else 0
     fabric = Fabric(devices="auto", strategy="ddp", plugins=QuantPrecision(mode, torch.bfloat16))
     fabric.launch()
     world, rank = fabric.world_size, fabric.global_rank
     assert fabric.device == torch.device("cuda", 0) and dist.get_backend() == "gloo"
-    cfg_kw = dict(n_layer=2, n_head=n_head, n_query_groups=n_groups, n_embd=128 * n_head, intermediate_size=256 * world * 2,
+    cfg_kw = dict(n_layer=2, n_head=n_head, n_query_groups=n_groups, n_embd=128 * n_head, intermediate_size=inter or 256 * world * 2,
                   padded_vocab_size=1024, vocab_size=1024, block_size=64)
     cfg = Config.from_name("Llama-2-7b-hf", **cfg_kw)
     rc = M.RefConfig.from_any(cfg)
@@ -93,6 +94,8 @@ def main() -> None:
         model.set_kv_cache(batch_size=1)
     model = fabric.to_device(model)
     assert model.tp_world_size == world and model.config.n_query_groups == n_groups // world
+    if inter and (inter // world) % 64:
+        assert model.transformer.h[0].mlp.proj.fold == 2 and model.transformer.h[0].mlp.proj.tiled is not None
 
     with torch.inference_mode():
         dev = fabric.device
@@ -100,13 +103,14 @@ def main() -> None:
         pw = oracle_tp_weights(p, mode, world)
         cos, sin = model.cos.cpu(), model.sin.cpu()
 
-        def run_oracle(dtype, c, s):
+        def run_oracle(dtype, c, s, forced=None):
             st = M.RefState(rc, n_total, 1, dtype, cos=c, sin=s)
-            toks, logits = M.generate(rc, {k: v.to(dtype) for k, v in pw.items()}, st, prompt, n_total, temperature=0.0, return_logits=True)
+            toks, logits = M.generate(rc, {k: v.to(dtype) for k, v in pw.items()}, st, prompt, n_total, temperature=0.0,
+                                      return_logits=True, forced=forced)
             return toks, logits.float()
 
         toks32, logits32 = run_oracle(torch.float32, cos.float(), sin.float())
-        _, logits16 = run_oracle(torch.bfloat16, cos, sin)
+        _, logits16 = run_oracle(torch.bfloat16, cos, sin, forced=toks32)  # same tokens: a rounding error, not a diverged rollout
         # ---- sharded CUDA path, teacher-forced along the oracle's tokens ---------------------------------------------
         got = [model(prompt.view(1, -1).to(dev), torch.arange(T, device=dev))[0, -1].float().cpu()]
         first = model(toks32[T].view(1, 1).to(dev), torch.tensor([T], device=dev))  # creates the peer communicator
