@@ -69,6 +69,7 @@ struct V4Params {
   int64_t tp_slot_stride;
   uint32_t* tp_recv_seq;
   uint32_t* tp_recv_done;
+  int wu, nwin;     // k-windows (batch > 1 whose activation rows do not fit shared memory): units per tile and window, window count
   int fold;         // row folding (b200_qgemv_tiled_args::fold): N, K, batch above are the FOLDED view; outputs are unfolded
   int64_t Nout;     // true output features (fold * N)
   int Kin;          // true input features (K / fold)
@@ -76,13 +77,13 @@ struct V4Params {
 };
 
 struct V4Plan {
-  uint32_t bars, red, ssq, rstd, xsum, xs, ringA, lut, ringC;
+  uint32_t bars, red, ssq, rstd, xsum, xs, tacc, ringA, lut, ringC;
   int nA, nC, S;
 };
 
 // Shared-memory carve-up by ABSOLUTE shared-window address (the table must sit at a 64 KB aligned address so that
 // `byte << 8 | lane << 2 | table` is one PRMT).  Shared by the kernel and the host-side feasibility check.
-__host__ __device__ inline V4Plan v4_plan(uint32_t b0, int stage, int red_bytes, bool int4, int B, int nkb, int xstride, int gap, int smem = kV4DynSmem) {
+__host__ __device__ inline V4Plan v4_plan(uint32_t b0, int stage, int red_bytes, bool int4, int B, int nkb, int xstride, int gap, int smem = kV4DynSmem, int extra = 0) {
   V4Plan pl{};
   uint32_t off = (b0 + 127u) & ~127u;
   pl.bars = off; off += 256;
@@ -91,6 +92,7 @@ __host__ __device__ inline V4Plan v4_plan(uint32_t b0, int stage, int red_bytes,
   pl.rstd = off; off += 64;
   pl.xsum = off; if (int4) off += (((uint32_t)(B * nkb) + 3u) & ~3u) * 4;
   pl.xs = off; if (!gap) off += (((uint32_t)B * xstride * 2) + 127u) & ~127u;
+  pl.tacc = off; off += (uint32_t)extra;
   off = (off + 127u) & ~127u;
   pl.ringA = off;
   const uint32_t end = b0 + (uint32_t)smem;
@@ -136,7 +138,7 @@ __device__ __forceinline__ float ld_cg_f32(const float* p) {
 // MODE 0: batch 1 (one accumulator column), MODE 1: batch <= 8, MODE 2: batch <= 16
 // XREG (batch 1, units per tile == consumer warps): a warp meets the same k-range in every unit, so its activation
 // fragments (and int4 block sums) stay in registers for the whole launch instead of being re-read from shared memory
-template <int RU, bool INT4, int MODE, bool XREG, int OCC = 1>
+template <int RU, bool INT4, int MODE, bool XREG, int OCC = 1, bool WIN = false>
 __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Params p) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   constexpr int NB = MODE == 2 ? 2 : 1;
@@ -152,7 +154,9 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
   const uint32_t b0 = smem_u32(smem_raw);
   uint8_t* const sb = smem_raw - b0;           // generic pointer to shared-window address 0
   const int B = p.batch;
-  const V4Plan pl = v4_plan(b0, STAGE, NBUF * kV4CW * REDW * 4, INT4, B, p.nkb, p.xstride, p.gap, OCC == 2 ? kV4DynSmem2 : kV4DynSmem);
+  // WIN: p.nkb / p.xstride describe ONE k-window; the per-tile accumulators of the reducer follow the activation rows
+  const int tacc_bytes = WIN ? ((((int)((p.U / (p.ts * p.upt)) + (int)gridDim.x - 1) / (int)gridDim.x) * p.ts) * 16 * COLS * 4) : 0;
+  const V4Plan pl = v4_plan(b0, STAGE, NBUF * kV4CW * REDW * 4, INT4, B, p.nkb, p.xstride, p.gap, OCC == 2 ? kV4DynSmem2 : kV4DynSmem, tacc_bytes);
   const int S = pl.S;
   if (S < 2) __trap();                         // the host sized the launch so that this cannot happen
   const uint32_t full_a = pl.bars, empty_a = pl.bars + 64, rfull_a = pl.bars + 128, rempty_a = pl.bars + 160;
@@ -186,6 +190,33 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
       const uint64_t pol = make_evict_first_policy();
       int n = 0, ps = 0;
       uint32_t pph = 1;           // parity to wait for on the slot's EMPTY barrier (first lap: no wait)
+      if constexpr (WIN) {
+        // window-major order: for every k-window, the window's units of every tile of this CTA; a stage never straddles
+        // a window boundary (the consumers swap the activation rows there)
+        const int ntl = t_last - t_first + 1;
+        for (int w = 0; w < p.nwin; ++w) {
+          const int wl = min(p.wu, upt - w * p.wu), tot = ntl * wl;
+          for (int j0 = 0; j0 < tot; j0 += kV4CW, ++n) {
+            if (n >= S) mbar_wait(empty_a + ps * 8, pph);
+            const int cnt = min(kV4CW, tot - j0);
+            const uint32_t bar = full_a + ps * 8;
+            uint32_t dst = stage_addr(ps);
+            mbar_expect_tx(bar, (uint32_t)cnt * UB);
+            int j = j0, rem = cnt;
+            while (rem > 0) {
+              const int tl = j / wl, kuw = j - tl * wl;
+              const int run = min(rem, wl - kuw);
+              const int tf = t_first + tl;
+              const uint8_t* src = (TS == 2 && (tf & 1)) ? p.tB : p.tA;
+              const int mt = TS == 2 ? (tf >> 1) : tf;
+              bulk_g2s(dst, src + ((int64_t)mt * upt + w * p.wu + kuw) * UB, (uint32_t)run * UB, bar, pol);
+              dst += (uint32_t)run * UB;
+              j += run; rem -= run;
+            }
+            if (++ps == S) { ps = 0; pph ^= 1u; }
+          }
+        }
+      } else
       for (int u = u0; u < u1; ++n) {
         if (n >= S) mbar_wait(empty_a + ps * 8, pph);
         const int cnt = min(kV4CW, u1 - u);
@@ -234,7 +265,78 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
           asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p.tp_peer_y[r] + (int64_t)c * p.Nout + n), "r"(pk) : "memory");
       }
     };
+    // epilogue of a complete entity (tile, or gate tile + up tile): bias / residual / SwiGLU / tensor-parallel packets
+    auto finish = [&](int e, float (&val)[2][NV]) {
+    if (p.epilogue == B200_EPI_SWIGLU) {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int o = MODE == 0 ? lane : 4 * lane + (i & 3) + 128 * (i >> 2);   // batch > 1: lane owns four consecutive outputs per 128
+        const int row = MODE == 0 ? (lane & 15) : o / COLS, c = MODE == 0 ? 0 : o % COLS;
+        const int64_t nrow = (int64_t)e * 16 + row;
+        if ((MODE != 0 || lane < 16) && c < B && nrow < p.N) {
+          const float a = round_bf16(val[0][i] + (p.bias ? __bfloat162float(p.bias[nrow]) : 0.f));
+          const float b = round_bf16(val[1][i] + (p.bias2 ? __bfloat162float(p.bias2[nrow]) : 0.f));
+          p.y[(int64_t)c * p.N + nrow] = __float2bfloat16_rn(silu_bf16_s(a) * b);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int o = MODE == 0 ? lane : 4 * lane + (i & 3) + 128 * (i >> 2);   // batch > 1: lane owns four consecutive outputs per 128
+        const int row = MODE == 0 ? (lane & 15) : o / COLS, c = MODE == 0 ? 0 : o % COLS;
+        const int64_t nrow = (int64_t)e * 16 + row;
+        if ((MODE != 0 || lane < 16) && c < B && nrow < p.N) store_out(nrow, c, val[0][i]);
+      }
+    }
+      };
     const int e_first = t_first / TS, e_last = t_last / TS;
+    if constexpr (WIN) {
+      // k-windows: the partial sums of (window, tile) arrive in window-major order and meet in this warp's per-tile
+      // accumulators (fixed order: deterministic); an entity is finished when its last window has arrived
+      const int ntl = t_last - t_first + 1, nq = p.nwin * ntl;
+      float* tacc = reinterpret_cast<float*>(sb + pl.tacc);
+      for (int q = 0; q < nq; ++q) {
+        const int w = q / ntl, tl = q - w * ntl;
+        const int buf = q % NBUF;
+        mbar_wait(rfull_a + buf * 8, (uint32_t)(q / NBUF) & 1u);
+        const float* rb = red + buf * (kV4CW * REDW);
+        float val[2][NV];
+#pragma unroll
+        for (int h = 0; h < NV / 4; ++h) {
+          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int ww = 0; ww < kV4CW; ++ww) {
+            const float4 q4 = *reinterpret_cast<const float4*>(rb + ww * REDW + 128 * h + 4 * lane);
+            v.x += q4.x; v.y += q4.y; v.z += q4.z; v.w += q4.w;
+          }
+          val[1][4 * h] = v.x; val[1][4 * h + 1] = v.y; val[1][4 * h + 2] = v.z; val[1][4 * h + 3] = v.w;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(rempty_a + buf * 8);
+        float* ta = tacc + tl * (16 * COLS);
+        if (w > 0) {
+#pragma unroll
+          for (int i = 0; i < NV; ++i) val[1][i] += ta[lane + 32 * i];
+        }
+        const int tf = t_first + tl;
+        const bool last = w == p.nwin - 1;
+        if (!last || (TS == 2 && !(tf & 1))) {   // not complete yet (or the gate tile waiting for its up tile): park it
+#pragma unroll
+          for (int i = 0; i < NV; ++i) ta[lane + 32 * i] = val[1][i];
+          continue;
+        }
+        if (TS == 2) {
+#pragma unroll
+          for (int i = 0; i < NV; ++i) val[0][i] = (ta - 16 * COLS)[lane + 32 * i];
+        } else {
+#pragma unroll
+          for (int i = 0; i < NV; ++i) val[0][i] = val[1][i];
+        }
+        finish(tf / TS, val);
+      }
+      if (lane == 0) v4_stamp(p, 5);
+      return;
+    }
     if (lane == 0 && p.debug != 3) v4_stamp(p, 7);
     int j = 0;  // tiles reduced so far (reduction-buffer sequence)
     for (int e = e_first; e <= e_last; ++e) {
@@ -260,11 +362,14 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
           val[which][0] = v;
         } else {
 #pragma unroll
-          for (int i = 0; i < NV; ++i) {
-            float v = 0.f;
+          for (int h = 0; h < NV / 4; ++h) {   // 128-bit loads: 2 x 16 (batch <= 8: 1 x 16) instead of 128 scalar ones
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int w = 0; w < kV4CW; ++w) v += rb[w * REDW + lane + 32 * i];
-            val[which][i] = v;
+            for (int w = 0; w < kV4CW; ++w) {
+              const float4 q4 = *reinterpret_cast<const float4*>(rb + w * REDW + 128 * h + 4 * lane);
+              v.x += q4.x; v.y += q4.y; v.z += q4.z; v.w += q4.w;
+            }
+            val[which][4 * h] = v.x; val[which][4 * h + 1] = v.y; val[which][4 * h + 2] = v.z; val[which][4 * h + 3] = v.w;
           }
         }
         __syncwarp();
@@ -315,28 +420,7 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
           if (lane == 0) *reinterpret_cast<volatile uint32_t*>(wsflag + c) = 0u;  // self-cleaning: ready for the next launch
         }
       }
-      // ---- epilogue of a complete entity --------------------------------------------------------------------------
-      if (p.epilogue == B200_EPI_SWIGLU) {
-#pragma unroll
-        for (int i = 0; i < NV; ++i) {
-          const int o = MODE == 0 ? lane : lane + 32 * i;
-          const int row = MODE == 0 ? (lane & 15) : o / COLS, c = MODE == 0 ? 0 : o % COLS;
-          const int64_t nrow = (int64_t)e * 16 + row;
-          if ((MODE != 0 || lane < 16) && c < B && nrow < p.N) {
-            const float a = round_bf16(val[0][i] + (p.bias ? __bfloat162float(p.bias[nrow]) : 0.f));
-            const float b = round_bf16(val[1][i] + (p.bias2 ? __bfloat162float(p.bias2[nrow]) : 0.f));
-            p.y[(int64_t)c * p.N + nrow] = __float2bfloat16_rn(silu_bf16_s(a) * b);
-          }
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < NV; ++i) {
-          const int o = MODE == 0 ? lane : lane + 32 * i;
-          const int row = MODE == 0 ? (lane & 15) : o / COLS, c = MODE == 0 ? 0 : o % COLS;
-          const int64_t nrow = (int64_t)e * 16 + row;
-          if ((MODE != 0 || lane < 16) && c < B && nrow < p.N) store_out(nrow, c, val[0][i]);
-        }
-      }
+      finish(e, val);
     }
     if (lane == 0) v4_stamp(p, 5);
     return;
@@ -383,6 +467,102 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
   if (p.tp_slots) rtag = (__ldcg(p.tp_recv_seq) % 65535u) + 1u;
   // ---- activation prologue: (x + delta) -> optional RMSNorm -> bf16 rows in shared memory -------------------------
   const bool designated = cta == 0;
+  constexpr int UK = RU * BPR * 64;            // k elements per unit
+  // WIN: stage window w of the activation rows: (x + delta) -> optional RMSNorm with the row's rstd -> bf16 in shared memory
+  auto add_bf16x8 = [](uint4 v, const uint4 dv) -> uint4 {
+    v.x = pack_bf16(bf16lo(v.x) + bf16lo(dv.x), bf16hi(v.x) + bf16hi(dv.x));
+    v.y = pack_bf16(bf16lo(v.y) + bf16lo(dv.y), bf16hi(v.y) + bf16hi(dv.y));
+    v.z = pack_bf16(bf16lo(v.z) + bf16lo(dv.z), bf16hi(v.z) + bf16hi(dv.z));
+    v.w = pack_bf16(bf16lo(v.w) + bf16lo(dv.w), bf16hi(v.w) + bf16hi(dv.w));
+    return v;
+  };
+  auto stage_window = [&](int w) {
+    const int k0 = w * p.wu * UK;
+    const int kw = min(p.wu * UK, (int)p.K - k0), wch = kw >> 3;
+    const int total = B * wch;                 // 16-byte chunks of the window, all rows: four loads in flight per thread
+    for (int i0 = tid; i0 < total; i0 += 4 * kV4Consumers) {
+      uint4 v[4], dv[4], nw[4];
+      int bb[4], cc[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * kV4Consumers;
+        bb[u] = i / wch; cc[u] = i - bb[u] * wch;
+        if (i < total) {
+          v[u] = *reinterpret_cast<const uint4*>(p.x + (int64_t)bb[u] * p.K + k0 + cc[u] * 8);
+          if (p.delta) dv[u] = *reinterpret_cast<const uint4*>(p.delta + (int64_t)bb[u] * p.K + k0 + cc[u] * 8);
+          if (p.norm_w) nw[u] = *reinterpret_cast<const uint4*>(p.norm_w + k0 + cc[u] * 8);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (i0 + u * kV4Consumers < total) {
+          uint4 x4 = v[u];
+          if (p.delta) x4 = add_bf16x8(x4, dv[u]);
+          if (p.norm_w) {
+            const float rstd = s_rstd[bb[u]];
+            const uint4 n4 = nw[u];
+            x4.x = pack_bf16(bf16lo(n4.x) * (bf16lo(x4.x) * rstd), bf16hi(n4.x) * (bf16hi(x4.x) * rstd));
+            x4.y = pack_bf16(bf16lo(n4.y) * (bf16lo(x4.y) * rstd), bf16hi(n4.y) * (bf16hi(x4.y) * rstd));
+            x4.z = pack_bf16(bf16lo(n4.z) * (bf16lo(x4.z) * rstd), bf16hi(n4.z) * (bf16hi(x4.z) * rstd));
+            x4.w = pack_bf16(bf16lo(n4.w) * (bf16lo(x4.w) * rstd), bf16hi(n4.w) * (bf16hi(x4.w) * rstd));
+          }
+          *reinterpret_cast<uint4*>(sb + pl.xs + (uint32_t)(bb[u] * p.xstride) * 2u + (uint32_t)cc[u] * 16u) = x4;
+        }
+      }
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
+    if (INT4) {   // per (row, k-block of the window) activation sums for the zero-point term (blocks past a short last window: unused)
+      xsum_blocks<kV4Consumers>(reinterpret_cast<const __nv_bfloat16*>(sb + pl.xs), p.xstride, B, p.nkb, xsum_s, tid);
+      asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
+    }
+  };
+  if constexpr (WIN) {
+    // pass 1 over the full rows: publish x + delta once, sum of squares -> rstd per row; the rows themselves are staged
+    // window by window in the main loop (same arithmetic and rounding points as the one-window path)
+    if (p.norm_w || (p.delta && p.x_out)) {
+      for (int b = 0; b < B; ++b) {
+        float ss = 0.f;
+        for (int c0 = tid; c0 < chunks; c0 += 4 * kV4Consumers) {   // four loads in flight per thread
+          uint4 v[4], dv[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int c = c0 + u * kV4Consumers;
+            if (c < chunks) {
+              v[u] = *reinterpret_cast<const uint4*>(p.x + (int64_t)b * p.K + c * 8);
+              if (p.delta) dv[u] = *reinterpret_cast<const uint4*>(p.delta + (int64_t)b * p.K + c * 8);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int c = c0 + u * kV4Consumers;
+            if (c < chunks) {
+              uint4 x4 = v[u];
+              if (p.delta) {
+                x4 = add_bf16x8(x4, dv[u]);
+                if (p.x_out && designated) *reinterpret_cast<uint4*>(p.x_out + (int64_t)b * p.K + c * 8) = x4;
+              }
+              const uint32_t w4[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+              for (int i = 0; i < 4; ++i) { const float a2 = bf16lo(w4[i]), c2 = bf16hi(w4[i]); ss = fmaf(a2, a2, ss); ss = fmaf(c2, c2, ss); }
+            }
+          }
+        }
+        if (p.norm_w) {
+          ss = warp_sum(ss);
+          if (lane == 0) s_ssq[warp * 16 + b] = ss;
+        }
+      }
+      if (p.norm_w) {
+        asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
+        if (tid < B) {
+          float tot = 0.f;
+#pragma unroll
+          for (int w = 0; w < kV4CW; ++w) tot += s_ssq[w * 16 + tid];
+          s_rstd[tid] = rsqrtf(tot / (float)p.K + p.eps);
+        }
+      }
+    }
+  } else
   if (B == 1 && !p.tp_slots && chunks <= 3 * kV4Consumers) {
     // batch-1 fast path (the decode chain): every load of the row is in flight at once, ONE pass over registers, the
     // sum of squares meets in shared memory with a single barrier and every thread derives rstd itself (same
@@ -453,6 +633,49 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
     }
     if (tid == 0 && p.debug == 3) v4_stamp_cyc(p, 7, c_rel);
   } else {
+    if (!p.tp_slots && p.fold <= 1) {
+      // batch > 1: the (row, chunk) items of this thread in row-major order, four global loads in flight at a time (a plain
+      // row loop serialises one L2 round trip per row: the shared-memory stores in between keep ptxas from hoisting loads)
+      const int ncm = (chunks + kV4Consumers - 1) / kV4Consumers, items = B * ncm;
+      float ss = 0.f;
+      for (int t0 = 0; t0 < items; t0 += 4) {
+        uint4 v[4], dv[4];
+        int bb[4], cc[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int t = t0 + u;
+          bb[u] = t / ncm; cc[u] = tid + (t - bb[u] * ncm) * kV4Consumers;
+          if (t < items && cc[u] < chunks) {
+            v[u] = *reinterpret_cast<const uint4*>(p.x + (int64_t)bb[u] * p.K + cc[u] * 8);
+            if (p.delta) dv[u] = *reinterpret_cast<const uint4*>(p.delta + (int64_t)bb[u] * p.K + cc[u] * 8);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int t = t0 + u;
+          if (t < items) {
+            if (cc[u] < chunks) {
+              uint4 x4 = v[u];
+              if (p.delta) {
+                x4 = add_bf16x8(x4, dv[u]);
+                if (p.x_out && designated) *reinterpret_cast<uint4*>(p.x_out + (int64_t)bb[u] * p.K + cc[u] * 8) = x4;
+              }
+              *reinterpret_cast<uint4*>(sb + xs_chunk(bb[u], cc[u])) = x4;
+              const uint32_t w4[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+              for (int i = 0; i < 4; ++i) { const float a2 = bf16lo(w4[i]), c2 = bf16hi(w4[i]); ss = fmaf(a2, a2, ss); ss = fmaf(c2, c2, ss); }
+            }
+            if (t - bb[u] * ncm == ncm - 1) {   // last item of the row (uniform across the CTA): the row's sum of squares
+              if (p.norm_w) {
+                ss = warp_sum(ss);
+                if (lane == 0) s_ssq[warp * 16 + bb[u]] = ss;
+              }
+              ss = 0.f;
+            }
+          }
+        }
+      }
+    } else
     for (int b = 0; b < B; ++b) {
       float ss = 0.f;
       for (int c = tid; c < chunks; c += kV4Consumers) {
@@ -543,7 +766,7 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
       *p.tp_recv_seq = __ldcg(p.tp_recv_seq) + 1u;
     }
   }
-  if (INT4) {       // per (batch row, k-block) activation sums for the zero-point term
+  if (INT4 && !WIN) {       // per (batch row, k-block) activation sums for the zero-point term
     xsum_blocks<kV4Consumers>(reinterpret_cast<const __nv_bfloat16*>(sb + pl.xs), p.xstride, B, p.nkb, xsum_s, tid);
     asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
   }
@@ -693,6 +916,52 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
     ++jf; ++ct;
   };
 
+  if constexpr (WIN) {
+    const int ntl = t_last - t_first + 1;
+    int s = 0, q_now = 0;        // ring slot; flush sequence (window * ntl + tile) the accumulators belong to
+    uint32_t ph = 0;
+    auto flush_to = [&](int q) { while (q_now < q) { flush(); ++q_now; } };
+    for (int w = 0; w < p.nwin; ++w) {
+      if (w > 0) asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");   // every warp is done with the previous window's rows
+      stage_window(w);
+      const int wl = min(p.wu, upt - w * p.wu), tot = ntl * wl;
+      for (int j0 = 0; j0 < tot; j0 += kV4CW) {
+        const int j = j0 + warp;
+        mbar_wait(full_a + s * 8, ph);
+        if (j < tot) {
+          const int tl = j / wl, kuw = j - tl * wl;
+          const uint32_t sp = stage_addr(s) + (uint32_t)warp * UB;
+          uint4 wv[RU][BPR];
+          uint2 sc[RU];
+#pragma unroll
+          for (int r = 0; r < RU; ++r) {
+#pragma unroll
+            for (int b = 0; b < BPR; ++b) {
+              const uint32_t wa = sp + r * REC + b * 512 + lane * 16;
+              asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(wv[r][b].x), "=r"(wv[r][b].y), "=r"(wv[r][b].z), "=r"(wv[r][b].w) : "r"(wa));
+            }
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(sc[r].x), "=r"(sc[r].y) : "r"(sp + r * REC + BPR * 512 + g * 8));
+          }
+          flush_to(w * ntl + tl);
+          if (p.debug != 1) {
+#pragma unroll
+            for (int r = 0; r < RU; ++r) {
+#pragma unroll
+              for (int b = 0; b < BPR; ++b) compute(wv[r][b], sc[r], (kuw * RU + r) * BPR + b, 0);
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_a + s * 8);
+        if (++s == S) { s = 0; ph ^= 1u; }
+      }
+      // hand in every partial sum of this window BEFORE the window barrier: a warp that kept its sums until its next unit
+      // would leave the reducer (and through the reduction buffers the other warps) waiting across that barrier -> deadlock
+      flush_to((w + 1) * ntl);
+    }
+    if (tid == 0 && p.debug != 3) v4_stamp(p, 4);
+    return;
+  }
   int u = u_first;
   int tf = tf_first, ku = ku_first;
   int s = 0;
@@ -762,9 +1031,23 @@ static cudaError_t launch_v4(const V4Params& p, int gx, cudaStream_t st) {
   return launch(qgemv_v4_kernel<RU, INT4, MODE, XREG>, dim3(gx), dim3(kV4Threads), (size_t)kV4DynSmem, st, p);
 }
 
+template <int RU, bool INT4, int MODE>
+static cudaError_t launch_v4_win(const V4Params& p, int gx, cudaStream_t st) {
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(qgemv_v4_kernel<RU, INT4, MODE, false, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kV4DynSmem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  return launch(qgemv_v4_kernel<RU, INT4, MODE, false, 1, true>, dim3(gx), dim3(kV4Threads), (size_t)kV4DynSmem, st, p);
+}
+
 template <bool INT4, int MODE>
 static cudaError_t launch_v4_ru(int ru, const V4Params& p, int gx, cudaStream_t st) {
   constexpr int RUMAX = INT4 ? 2 : 4;
+  if constexpr (MODE != 0) {
+    if (p.nwin > 1) return ru == RUMAX ? launch_v4_win<RUMAX, INT4, MODE>(p, gx, st) : launch_v4_win<1, INT4, MODE>(p, gx, st);
+  }
   if (ru == RUMAX) {
     if constexpr (MODE == 0 && INT4) {
       if (g_v4_occ2.load()) return launch_v4_occ2<RUMAX, true>(p, gx, st);
@@ -806,9 +1089,33 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
     const V4Plan pl = v4_plan(1024u, stage, red_bytes, int4, a->batch, nkb, xstride, gap, (int4 && mode == 0 && g_v4_occ2.load()) ? kV4DynSmem2 : kV4DynSmem);
     if (pl.S >= 2) { ru = cand; break; }
   }
-  if (ru == 0) return B200_ERR_UNSUPPORTED;
   const int64_t ntiles = (a->N + 15) / 16;
   const int ts = swiglu ? 2 : 1;
+  // k-windows: batch > 1 whose full activation rows leave no room for the ring.  The rows are staged one window of `wu`
+  // units at a time; the CTA sweeps its tiles once per window and the reducer keeps per-tile partial sums.
+  int wu = 0, nwin = 1, win_nkb = 0, win_xstride = 0;
+  if (ru == 0 && mode != 0 && fold == 1 && !(a->tp && a->tp->slots)) {
+    int sms = sm_count();
+    if (sms > kV4MaxCtas) sms = kV4MaxCtas;
+    const int64_t gxw = ntiles < sms ? ntiles : sms;
+    const int extra = (int)(((ntiles + gxw - 1) / gxw) * ts) * 16 * cols * 4;
+    // fewest windows first (each costs a barrier pair, a reload of the rows and a round of partial sums): the largest window
+    // that leaves two ring stages; the windows are then equalised, which usually frees room for a third stage
+    for (int cand = int4 ? 2 : 4; cand >= 1 && ru == 0; cand = cand > 1 ? 1 : 0) {   // the largest unit, then single records
+      if (nrec % cand) continue;
+      const int upt_c = nrec / cand, uk = cand * (int4 ? 128 : 64), stage = kV4CW * cand * (int4 ? 1088 : 576);
+      for (int w = upt_c - 1; w >= 1; --w) {
+        const V4Plan pl = v4_plan(1024u, stage, red_bytes, int4, a->batch, w * uk / 64, w * uk + 8, 0, kV4DynSmem, extra);
+        if (pl.S >= 2) {
+          nwin = (upt_c + w - 1) / w;
+          wu = (upt_c + nwin - 1) / nwin;      // equal windows
+          ru = cand; win_nkb = wu * uk / 64; win_xstride = wu * uk + 8;
+          break;
+        }
+      }
+    }
+  }
+  if (ru == 0) return B200_ERR_UNSUPPORTED;
   const int64_t U = ntiles * ts * (nrec / ru);
   if (U <= 0 || U > 0x3fffffff) return B200_ERR_UNSUPPORTED;
   if (dry) return B200_OK;
@@ -828,6 +1135,8 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
   p.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual);
   p.y = reinterpret_cast<__nv_bfloat16*>(a->y);
   p.xstride = xstride; p.gap = gap;
+  p.wu = wu; p.nwin = nwin;
+  if (nwin > 1) { p.nkb = win_nkb; p.xstride = win_xstride; }
   p.fold = fold; p.Nout = a0->N; p.Kin = (int)a0->K;
   p.ws = reinterpret_cast<uint8_t*>(a->workspace);
   if (a->tp) {
@@ -851,7 +1160,7 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
   // (~2 us exposed: fence + flag + two L2 round trips): bytes of imbalance at ~6 TB/s.
   const int64_t E = ntiles;                       // entities (tiles, or gate/up pairs)
   const int64_t ent_bytes = (int64_t)ts * nrec * (int4 ? 1088 : 576);
-  const int force = g_v4_split.load();
+  const int force = nwin > 1 ? 0 : g_v4_split.load();   // k-windows keep whole entities per CTA
   if (E >= gx) {
     const double waste_us = (double)(((E + gx - 1) / gx) * gx - E) / gx * ent_bytes / 6.0e6;   // idle share of the last wave
     p.split = force >= 0 ? force : (waste_us > 2.5 ? 1 : 0);

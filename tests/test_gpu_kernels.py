@@ -125,6 +125,45 @@ def test_qgemv_tuning_variants_agree(K, ks, occ):
     _check_gemv(y, x.float(), deq)
 
 
+@pytest.mark.parametrize("qt", ["nf4", "int4"])
+@pytest.mark.parametrize("N,Kdim,B", [(5120, 13824, 16), (2048, 13824, 8), (1000, 5120, 16), (640, 8192, 16), (5120, 13824, 9), (96, 28672, 16)])
+def test_qgemv_tiled_k_windows(K, qt, N, Kdim, B):
+    """Batch x K too large for the activation rows to sit in shared memory beside the ring (Llama-2-13B gptq.int4 at batch
+    16, BASELINE config 3): the kernel sweeps its tiles once per k-window.  Plain, norm + delta prologue with the residual
+    epilogue, and the SwiGLU pair, against the oracle's dequantised weights."""
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, B, qt, seed=N + B)
+    tiled = K.tile_4bit(packed, scale, N, Kdim, qt, bs)
+    assert K.qgemv_tiled_supported(N, Kdim, qt, B)
+    y = K.qgemv_tiled(x.cuda(), tiled, N, Kdim, qt, bs)
+    _check_gemv(y, x.float(), deq)
+    assert torch.equal(y, K.qgemv_tiled(x.cuda(), tiled, N, Kdim, qt, bs)), "not deterministic"
+    # prologue: (x + delta) -> x_out, RMSNorm; epilogue: residual
+    delta, nw, res = _randw((B, Kdim), 3, std=1.0), _randw((Kdim,), 4, std=1.0), _randw((B, N), 5, std=1.0)
+    x_out = torch.empty(B, Kdim, dtype=torch.bfloat16, device="cuda")
+    y2 = K.qgemv_tiled(x.cuda(), tiled, N, Kdim, qt, bs, delta=delta.cuda(), x_out=x_out, norm_weight=nw.cuda(), norm_eps=1e-5, residual=res.cuda())
+    xs = (x + delta)  # bf16 add, as `x = h + x` in the reference (model.py:591)
+    assert torch.equal(x_out.cpu(), xs)
+    xn = M.rmsnorm(xs, nw, 1e-5)  # oracle rounding points (rmsnorm.py:19-25)
+    _check_gemv(y2, xn.float(), deq, post=lambda t: t.to(torch.bfloat16).float() + res.float())
+
+
+@pytest.mark.parametrize("qt", ["nf4", "int4"])
+def test_qgemv_tiled_k_windows_swiglu(K, qt):
+    N, Kdim, B = 1376, 8192, 16
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, B, qt, seed=11)
+    w2, _, packed2, scale2, _, deq2 = _gemv_case(K, N, Kdim, B, qt, seed=12)
+    t1, t2 = K.tile_4bit(packed, scale, N, Kdim, qt, bs), K.tile_4bit(packed2, scale2, N, Kdim, qt, bs)
+    assert K.qgemv_tiled_supported(N, Kdim, qt, B, True)
+    y = K.qgemv_tiled(x.cuda(), t1, N, Kdim, qt, bs, tiled2=t2).float().cpu()
+    xb = x.to(torch.bfloat16).cuda()
+    a = torch.nn.functional.linear(xb, deq.to(torch.bfloat16).cuda())
+    b = torch.nn.functional.linear(xb, deq2.to(torch.bfloat16).cuda())
+    comp = (torch.nn.functional.silu(a) * b).float().cpu()
+    wide = (torch.nn.functional.silu(x.double() @ deq.double().T) * (x.double() @ deq2.double().T)).float()
+    e_k, e_t = (y - wide).abs().max().item(), (comp - wide).abs().max().item()
+    assert e_k <= 2.0 * e_t + 2 ** -8 * wide.abs().max().item(), (e_k, e_t)
+
+
 @pytest.mark.parametrize("qt", ["nf4", "fp4"])
 @pytest.mark.parametrize("N,Kdim,B,fold", [(4096, 1376, 1, 2), (256, 96, 3, 2), (512, 1376, 8, 2), (64, 48, 2, 4), (4096, 1376, 4, 2)])
 def test_qgemv_tiled_folded_rows(K, qt, N, Kdim, B, fold):
@@ -488,9 +527,9 @@ def test_qgemv_tiled_bias_and_errors(K):
     assert (y.float().cpu() - want).abs().max() <= 2 ** -6 * want.abs().max()
     with pytest.raises(B200Error, match="batch"):
         K.qgemv_tiled(torch.zeros(17, 512, dtype=torch.bfloat16, device="cuda"), tiled, 256, 512, "nf4", bs)
-    with pytest.raises(NotImplementedError, match="shared memory"):
-        K.qgemv_tiled(torch.zeros(16, 8192, dtype=torch.bfloat16, device="cuda"),
-                      torch.zeros(K.tiled_bytes(16, 8192, "nf4"), dtype=torch.uint8, device="cuda"), 16, 8192, "nf4", bs)
+    # activation rows that do not fit beside the ring run through k-windows now (test_qgemv_tiled_k_windows); the tensor-
+    # parallel consumer is the one remaining shape outside every plan and must say so without launching anything
+    assert K.qgemv_tiled_supported(16, 8192, "nf4", 16) and not K.qgemv_tiled_supported(16, 8192, "nf4", 17)
 
 
 def test_qgemv_tiled_onehot_reads_dequantised_column(K):

@@ -191,17 +191,23 @@ def test_sampling_path_in_graph(golden):
     assert cut.tolist() == greedy[: first + 1].tolist()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_tp2_matches_single_gpu(tmp_path):
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (the one-GPU variant is tests/test_gpu_tp_shared.py)")
+@pytest.mark.parametrize("mode,inter", [("nf4", 0), ("int4", 0), ("nf4", 2112)])
+def test_tp2_matches_oracle_multi_gpu(mode, inter):
+    """Two ranks on two GPUs over NCCL / NVLink: the sharded model (peer-memory hand-off in the GEMVs) against the oracle on
+    identically sharded-then-quantized weights, identical logits on every rank, and agreement with the all-NCCL path
+    (B200_TP_NCCL=1).  inter = 2112: the mlp.proj shard (1056 columns) is not block-aligned -> folded tiled layout."""
     import os
     import subprocess
     import sys
 
     root = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+    env = dict(os.environ, B200_TP_SHARED_DEVICE="0", B200_TP_NCCL="0", OMP_NUM_THREADS="4")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-           "--master-port", "29631", os.path.join(root, "tests", "tp_gpu_worker.py"), root]
-    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
-    assert out.returncode == 0 and "TP_GPU_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+           "--master-port", "29631", os.path.join(root, "tests", "tp_shared_worker.py"), root, mode, "8", "4", "0", str(inter)]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert out.returncode == 0 and "TP_SHARED_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+    print(out.stdout[-500:])
 
 
 @torch.inference_mode(False)

@@ -70,7 +70,11 @@ def main() -> None:
     fabric = Fabric(devices="auto", strategy="ddp", plugins=QuantPrecision(mode, torch.bfloat16))
     fabric.launch()
     world, rank = fabric.world_size, fabric.global_rank
-    assert fabric.device == torch.device("cuda", 0) and dist.get_backend() == "gloo"
+    shared = os.environ.get("B200_TP_SHARED_DEVICE", "0") == "1"
+    if shared:
+        assert fabric.device == torch.device("cuda", 0) and dist.get_backend() == "gloo"
+    else:  # one GPU per rank, NCCL control plane (tests/test_gpu_model.py::test_tp2_matches_oracle_multi_gpu)
+        assert fabric.device == torch.device("cuda", fabric.local_rank) and dist.get_backend() == "nccl"
     cfg_kw = dict(n_layer=2, n_head=n_head, n_query_groups=n_groups, n_embd=128 * n_head, intermediate_size=inter or 256 * world * 2,
                   padded_vocab_size=1024, vocab_size=1024, block_size=64)
     cfg = Config.from_name("Llama-2-7b-hf", **cfg_kw)
@@ -138,8 +142,9 @@ def main() -> None:
         agree = got.argmax(-1) == logits32.argmax(-1)
         assert bool(agree[decisive].all()), agree.tolist()
         # ---- every rank holds the same logits bit for bit (no broadcast in tp.py:200) ----------------------------------
-        gathered = [torch.empty_like(got) for _ in range(world)]
-        dist.all_gather(gathered, got)
+        got_d = got if shared else got.to(dev)   # gloo gathers host tensors, NCCL device tensors
+        gathered = [torch.empty_like(got_d) for _ in range(world)]
+        dist.all_gather(gathered, got_d)
         assert all(torch.equal(gathered[0], t) for t in gathered)
         # ---- free-running generate(): the captured decode graph with the hand-offs inside ---------------------------
         for blk in model.transformer.h:
@@ -149,14 +154,31 @@ def main() -> None:
         div = next((i for i in range(T, n_total) if out[i].item() != toks32[i].item()), None)
         if div is not None:
             assert not bool(decisive[div - T]), f"rollout diverged at decisive step {div}"
-        outs = [torch.empty_like(out) for _ in range(world)]
-        dist.all_gather(outs, out)
+        out_d = out if shared else out.to(dev)
+        outs = [torch.empty_like(out_d) for _ in range(world)]
+        dist.all_gather(outs, out_d)
         assert all(torch.equal(outs[0], t) for t in outs)
+        e_n = None
+        if not shared:
+            # the same sharded model with every row-parallel sum by NCCL all-reduce (generate/tp.py:73-74): the peer-memory
+            # hand-off must agree with it to bf16 rounding of the partial sums
+            os.environ["B200_TP_NCCL"] = "1"
+            model.__dict__.pop("_p2p", None)
+            model.__dict__.pop("_decode_graphs", None)
+            for blk in model.transformer.h:
+                blk.attn.kv_cache.reset_parameters()
+            model(prompt.view(1, -1).to(dev), torch.arange(T, device=dev))
+            d_nccl = model(toks32[T].view(1, 1).to(dev), torch.tensor([T], device=dev))[0, -1].float().cpu()
+            assert model.__dict__.get("_p2p") is False
+            os.environ["B200_TP_NCCL"] = "0"
+            e_n = (d_nccl - got[1]).abs().max().item()
+            assert e_n <= 2 ** -6 * scale, (e_n, scale)
         seq_now = int(raw_u32(comm._flags(comm._local, 0), 1, dev).item())
     if rank == 0:
-        print(f"[tp{world}/shared-gpu/{mode}/H{n_head}G{n_groups}] bf16-reference err {e_ref:.4f} cuda err {e_k:.4f} tol {tol:.4f} "
+        print(f"[tp{world}/{'shared-gpu' if shared else 'multi-gpu'}/{mode}/H{n_head}G{n_groups}/I{cfg.intermediate_size}] bf16-reference err {e_ref:.4f} cuda err {e_k:.4f} tol {tol:.4f} "
               f"(|logit| max {scale:.2f}); top-1 {int(agree.sum())}/{len(agree)} (decisive {int(decisive.sum())}); "
-              f"greedy prefix {(div or n_total) - T}/{n_total - T}; hand-off seq {seq0} -> {seq_now}", flush=True)
+              f"greedy prefix {(div or n_total) - T}/{n_total - T}; hand-off seq {seq0} -> {seq_now}"
+              + ("" if e_n is None else f"; |p2p - nccl| {e_n:.4f}"), flush=True)
     if seq0:
         assert seq_now > seq0 and (seq0 % 65535) > (seq_now % 65535), "the run was meant to cross the tag wrap-around"
     torch.cuda.synchronize()
