@@ -153,6 +153,114 @@ def test_llama7b_width_two_layers_nf4():
 
 
 @torch.inference_mode()
+def test_mistral7b_width_two_layers_int4_gqa():
+    """Mistral-7B shapes (d = 4096, 32 heads / 8 KV groups, I = 14336, BASELINE config 4) at depth 2, gptq.int4: the grouped-
+    query decode kernel, the int4 streaming GEMV at K = 14336 and the prefill GEMM, end to end against the oracle."""
+    from lit_gpt_b200 import Config
+    from lit_gpt_b200.config import name_to_config
+
+    cfg = Config.from_name("Mistral-7B-v0.1", n_layer=2)
+    rc = M.RefConfig.from_any(cfg)
+    p = M.init_weights(rc, seed=77, dtype=torch.bfloat16)
+    kw = dict(name_to_config["Mistral-7B-v0.1"], n_layer=2)
+    model = build_cuda_model(kw, p, "int4", max_seq=48)
+    assert model.fused_decode_ready() and model.config.n_query_groups == 8
+    blk = model.transformer.h[0]
+    assert all(l.streams(1) for l in (blk.attn.attn, blk.attn.proj, blk.mlp.proj, model.lm_head)) and blk.mlp.fc_1.streams(1, swiglu=True)
+    pw = oracle_weights(p, "int4")
+    g = torch.Generator().manual_seed(4)
+    prompt = torch.randint(0, cfg.vocab_size, (12,), generator=g)
+    check_rollout(model, rc, pw, prompt, 36, "mistral7b-width-2L/int4")
+
+
+@pytest.mark.parametrize("B", [4, 16])
+@torch.inference_mode()
+def test_llama13b_width_batched_decode_int4(B):
+    """Llama-2-13B shapes (d = 5120, I = 13824, BASELINE config 3) at depth 2, gptq.int4, batch 4 and 16: every row of the
+    batched decode step (streaming GEMV: k-windows at batch 16) against the oracle run row by row."""
+    from lit_gpt_b200 import Config
+    from lit_gpt_b200.config import name_to_config
+
+    cfg = Config.from_name("Llama-2-13b-hf", n_layer=2)
+    rc = M.RefConfig.from_any(cfg)
+    p = M.init_weights(rc, seed=13, dtype=torch.bfloat16)
+    kw = dict(name_to_config["Llama-2-13b-hf"], n_layer=2)
+    model = build_cuda_model(kw, p, "int4", max_seq=16, batch=B)
+    assert model.fused_decode_ready()
+    blk = model.transformer.h[0]
+    assert all(l.streams(B) for l in (blk.attn.attn, blk.attn.proj, blk.mlp.proj, model.lm_head)) and blk.mlp.fc_1.streams(B, swiglu=True)
+    pw = oracle_weights(p, "int4")
+    g = torch.Generator().manual_seed(5)
+    T = 6
+    prompts = torch.randint(0, cfg.vocab_size, (B, T), generator=g)
+    nxt = torch.randint(0, cfg.vocab_size, (B, 1), generator=g)
+    model(prompts.cuda(), torch.arange(T, device="cuda"))
+    got = model(nxt.cuda(), torch.tensor([T], device="cuda"))[:, -1].float().cpu()   # one fused decode step, B rows
+    cos, sin = model.cos.cpu(), model.sin.cpu()
+    rows = [0, B // 2, B - 1] if B > 4 else list(range(B))
+    for r in rows:
+        outs = {}
+        for dtype, c, s_ in ((torch.float32, cos.float(), sin.float()), (torch.bfloat16, cos, sin)):
+            st = M.RefState(rc, 16, 1, dtype, cos=c, sin=s_)
+            pd = {k: v.to(dtype) for k, v in pw.items()}
+            M.gpt_forward(rc, pd, prompts[r : r + 1], torch.arange(T), st)
+            outs[dtype] = M.gpt_forward(rc, pd, nxt[r : r + 1], torch.tensor([T]), st)[0, -1].float()
+        scale = outs[torch.float32].abs().max().item()
+        e_ref = (outs[torch.bfloat16] - outs[torch.float32]).abs().max().item()
+        e_k = (got[r] - outs[torch.float32]).abs().max().item()
+        tol = 2.0 * e_ref + 1e-3 * scale
+        print(f"[llama13b-width-2L/int4/B={B}/row {r}] bf16-reference err={e_ref:.4f} cuda err={e_k:.4f} tol={tol:.4f}")
+        assert e_k <= tol, (r, e_k, tol)
+
+
+@torch.inference_mode()
+def test_long_context_rollout_bf16_rope_tables(golden):
+    """A rollout past position 256 with the reference's bf16-default RoPE tables (build_rope_cache runs under the
+    bf16 default dtype in generate/base.py, so the tables themselves are bf16): the decode attention's split / cluster paths at
+    a context of ~300 and the table handling, against the oracle using the same tables."""
+    g = golden("llama_mha_hs128")
+    cfgd, kw = cfg_from_golden(g)
+    kw = dict(kw, block_size=512)
+    cfgd = dict(cfgd, block_size=512)
+    rc = M.RefConfig.from_any(cfgd)
+    p = M.init_weights(rc, seed=99)
+    model = build_cuda_model(kw, p, "nf4", max_seq=330)
+    # generate/base.py builds the tables under the bf16 default dtype: bf16 tables (positions past 256 are not bf16-exact)
+    model.cos, model.sin = model.cos.to(torch.bfloat16), model.sin.to(torch.bfloat16)
+    model.__dict__.pop("_decode_graphs", None)
+    pw = oracle_weights(p, "nf4")
+    gen = torch.Generator().manual_seed(6)
+    prompt = torch.randint(0, cfgd["vocab_size"], (280,), generator=gen)
+    check_rollout(model, rc, pw, prompt, 310, "long-context/nf4")
+
+
+@torch.inference_mode()
+def test_chat_stream_matches_generate(golden):
+    """chat/base.py:24-68 on the fused path: the streamed tokens are generate()'s tokens, and a stop sequence ends the stream
+    without being emitted."""
+    import lit_gpt_b200.chat.base as chat
+    import lit_gpt_b200.generate.base as gb
+
+    g = golden("llama_gqa_hs64")
+    cfgd, kw = cfg_from_golden(g)
+    p = M.init_weights(M.RefConfig.from_any(cfgd), seed=1234)
+    model = build_cuda_model(kw, p, "nf4", max_seq=40)
+    prompt = torch.from_numpy(g["gen_prompt"]).cuda()
+    T = prompt.numel()
+    full = gb.generate(model, prompt, 30, temperature=0.0)
+    for blk in model.transformer.h:
+        blk.attn.kv_cache.reset_parameters()
+    stream = torch.cat(list(chat.generate(model, prompt, 30, temperature=0.0)))
+    assert torch.equal(stream, full[T:])
+    stop = [int(full[T + 9])]   # (multi-token hold-back rules: the reference's own vectors in tests/test_chat_cpu.py)
+    first = next(i for i in range(T, 30) if int(full[i]) == stop[0])
+    for blk in model.transformer.h:
+        blk.attn.kv_cache.reset_parameters()
+    cut = list(chat.generate(model, prompt, 30, temperature=0.0, stop_tokens=(stop,)))
+    assert (torch.cat(cut).tolist() if cut else []) == full[T:first].tolist()
+
+
+@torch.inference_mode()
 def test_batched_decode_matches_single(golden):
     """batch 1/4/16 at the model level (generate() is batch-1): rows are independent."""
     g = golden("llama_mha_hs128")
