@@ -305,6 +305,8 @@ def run_ours(args) -> None:
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py (impl ours) needs a CUDA device: the product path has no CPU fallback")
+    if os.environ.get("B200_TUNE_OCC"):  # development: A/B switches of b200_qgemv_tiled_tune (e.g. 14 = no K / V cache L2 hint)
+        K.qgemv_tiled_tune(0, int(os.environ["B200_TUNE_OCC"]), False)
     cfg_name, mode, batch, T, ctx = WORKLOADS[args.workload]
     world = int(os.environ.get("WORLD_SIZE", 1))
     if world != args.gpus:

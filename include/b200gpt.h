@@ -145,6 +145,21 @@ int b200_p2p_open(const void* handle64, void** ptr);
 int b200_p2p_close(void* ptr);
 int b200_p2p_free(void* ptr);
 
+/* Optional hint for the launch that precedes a decode-attention step (the fused QKV projection): once its own weight stream
+ * has been issued, the kernel asks the L2 for the filled part of this layer's K / V cache (cp.async.bulk.prefetch.L2), so that
+ * the attention kernel's dependent loads hit L2 instead of HBM.  `chunks` = batch * n_query_groups contiguous (Tmax, hs) planes
+ * per tensor, `chunk_stride` bytes apart; rows [0, *pos) of `row_bytes` each are fetched.  A hint only: no effect on results. */
+typedef struct b200_kv_hint {
+  const void* k;
+  const void* v;
+  const void* pos;       /* device scalar, int32 or int64 */
+  int pos_is_int64;
+  int chunks;
+  int64_t chunk_stride;
+  int row_bytes;
+  int max_rows;
+} b200_kv_hint;
+
 typedef struct b200_qgemv_tiled_args {
   const void* tiled;
   const void* tiled2;      /* second matrix for SWIGLU, else NULL */
@@ -168,6 +183,7 @@ typedef struct b200_qgemv_tiled_args {
                               partial sums / arrival counters of row pairs cut by a stream-K boundary (self-cleaning) */
   size_t workspace_bytes;
   const struct b200_tp_handoff* tp; /* optional tensor-parallel hand-off (below); NULL on one GPU */
+  const b200_kv_hint* kv_hint; /* optional (above); NULL = none */
   int fold;                /* 0 / 1: plain.  F = 2, 4: `tiled` holds the matrix VIEWED as (N / F, F * K), i.e. b200_tile_4bit(N / F, F * K)
                               of the same flat nf4 / fp4 buffers: for row-parallel shards whose K is not a multiple of the
                               64-element block while F * K is (generate/tp.py:28-45 cuts mlp.proj to 11008 / 8 = 1376 columns, and

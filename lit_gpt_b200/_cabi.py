@@ -41,6 +41,11 @@ class TpHandoff(ctypes.Structure):  # mirrors b200_tp_handoff
                 ("slots", c_void_p), ("slot_stride", c_int64), ("recv_seq", c_void_p), ("recv_done", c_void_p)]
 
 
+class KvHint(ctypes.Structure):
+    _fields_ = [("k", c_void_p), ("v", c_void_p), ("pos", c_void_p), ("pos_is_int64", c_int), ("chunks", c_int),
+                ("chunk_stride", c_int64), ("row_bytes", c_int), ("max_rows", c_int)]
+
+
 class QGemvTiledArgs(ctypes.Structure):
     _fields_ = [
         ("tiled", c_void_p), ("tiled2", c_void_p), ("qtype", c_int), ("blocksize", c_int), ("N", c_int64), ("K", c_int64),
@@ -48,7 +53,7 @@ class QGemvTiledArgs(ctypes.Structure):
         ("norm_eps", c_float), ("batch", c_int), ("epilogue", c_int),
         ("bias", c_void_p), ("bias2", c_void_p), ("residual", c_void_p), ("y", c_void_p),
         ("prefetch", c_void_p), ("prefetch_bytes", c_int64), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
-        ("tp", ctypes.POINTER(TpHandoff)), ("fold", c_int),
+        ("tp", ctypes.POINTER(TpHandoff)), ("kv_hint", ctypes.POINTER(KvHint)), ("fold", c_int),
     ]
 
 

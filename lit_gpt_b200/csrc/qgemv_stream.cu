@@ -582,7 +582,8 @@ int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch) {
   g_stream_occ = ctas_per_sm;
   // development knobs: 10 = never split entities, 11 = always, 12 = no register-resident activations
   qgemv_v4_tune(ctas_per_sm == 11 ? 1 : ctas_per_sm == 10 ? 0 : -1, ctas_per_sm == 12 ? 0 : 1);
-  qgemv_v4_tune_occ2(ctas_per_sm == 13 ? 1 : 0);   // 13: int4 batch-1 as two co-resident CTAs per SM (experiment)
+  qgemv_v4_tune_occ2(ctas_per_sm == 13 ? 1 : 0);
+  qgemv_v4_tune_kvhint(ctas_per_sm == 14 ? 0 : 1);   // 14: ignore the K / V cache L2 hint   // 13: int4 batch-1 as two co-resident CTAs per SM (experiment)
   g_stream_pf = l2_prefetch;
   return B200_OK;
 }

@@ -69,6 +69,8 @@ struct V4Params {
   int64_t tp_slot_stride;
   uint32_t* tp_recv_seq;
   uint32_t* tp_recv_done;
+  const uint8_t* kvh_k; const uint8_t* kvh_v; const void* kvh_pos;   // K / V cache L2 hint (b200_kv_hint), kvh_k == NULL: none
+  int kvh_i64, kvh_chunks, kvh_row, kvh_max; long long kvh_stride;
   int wu, nwin;     // k-windows (batch > 1 whose activation rows do not fit shared memory): units per tile and window, window count
   int fold;         // row folding (b200_qgemv_tiled_args::fold): N, K, batch above are the FOLDED view; outputs are unfolded
   int64_t Nout;     // true output features (fold * N)
@@ -237,6 +239,17 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
         if (++ps == S) { ps = 0; pph ^= 1u; }
       }
       if (p.debug != 3) v4_stamp(p, 6);
+      if (p.kvh_k) {
+        // this launch's weight stream is issued: ask the L2 for the filled rows of the K / V cache the attention kernel reads
+        // next (one plane per CTA).  pos may lag by one step here (no dependency wait on this path): it is only a hint
+        for (int c = cta; c < 2 * p.kvh_chunks; c += G) {
+          long long pos = p.kvh_i64 ? *reinterpret_cast<const volatile long long*>(p.kvh_pos) : (long long)*reinterpret_cast<const volatile int*>(p.kvh_pos);
+          if (pos > p.kvh_max) pos = p.kvh_max;
+          const long long bytes = pos * p.kvh_row;
+          const uint8_t* base = (c < p.kvh_chunks ? p.kvh_k : p.kvh_v) + (long long)(c % p.kvh_chunks) * p.kvh_stride;
+          for (long long o = 0; o < bytes; o += 65536) prefetch_l2_bulk(base + o, (uint32_t)(bytes - o < 65536 ? ((bytes - o + 15) & ~15LL) : 65536));
+        }
+      }
     }
     griddep_launch();
     return;
@@ -1004,10 +1017,12 @@ static int g_v4_trace_slots = 0, g_v4_trace_next = 0;
 void qgemv_v4_set_trace(void* buf, int slots) { g_v4_trace = reinterpret_cast<unsigned long long*>(buf); g_v4_trace_slots = slots; g_v4_trace_next = 0; }
 
 static std::atomic<int> g_v4_occ2{0};     // experiment: int4 batch-1 launches as two co-resident CTAs per SM
+static std::atomic<int> g_v4_kvhint{1};   // K / V cache L2 hint honoured (tune knob 14 switches it off)
 static std::atomic<int> g_v4_split{-1};   // -1 auto, 0 never split entities, 1 always
 static std::atomic<int> g_v4_xreg{1};     // activation fragments in registers where the shape allows
 void qgemv_v4_tune(int split, int xreg) { g_v4_split = split; g_v4_xreg = xreg; }
 void qgemv_v4_tune_occ2(int on) { g_v4_occ2 = on; }
+void qgemv_v4_tune_kvhint(int on) { g_v4_kvhint = on; }
 
 template <int RU, bool INT4>
 static cudaError_t launch_v4_occ2(const V4Params& p, int gx, cudaStream_t st) {
@@ -1138,6 +1153,11 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
   p.wu = wu; p.nwin = nwin;
   if (nwin > 1) { p.nkb = win_nkb; p.xstride = win_xstride; }
   p.fold = fold; p.Nout = a0->N; p.Kin = (int)a0->K;
+  if (a0->kv_hint && a0->kv_hint->k && a0->kv_hint->v && a0->kv_hint->pos && g_v4_kvhint.load()) {
+    const b200_kv_hint* h = a0->kv_hint;
+    p.kvh_k = reinterpret_cast<const uint8_t*>(h->k); p.kvh_v = reinterpret_cast<const uint8_t*>(h->v); p.kvh_pos = h->pos;
+    p.kvh_i64 = h->pos_is_int64; p.kvh_chunks = h->chunks; p.kvh_row = h->row_bytes; p.kvh_max = h->max_rows; p.kvh_stride = h->chunk_stride;
+  }
   p.ws = reinterpret_cast<uint8_t*>(a->workspace);
   if (a->tp) {
     const b200_tp_handoff* h = a->tp;

@@ -13,5 +13,6 @@ void qgemv_v4_tune(int split, int xreg);
 // development: per-CTA phase time stamps (globaltimer) of the next `slots` launches into buf[slots][160][8] (u64); NULL = off
 void qgemv_v4_set_trace(void* buf, int slots);
 void qgemv_v4_tune_occ2(int on);
+void qgemv_v4_tune_kvhint(int on);
 
 }  // namespace b200

@@ -273,7 +273,7 @@ def qgemv_tiled(x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, quant_type
                 x_out: Optional[torch.Tensor] = None, norm_weight: Optional[torch.Tensor] = None, norm_eps: float = 1e-5,
                 residual: Optional[torch.Tensor] = None, tiled2: Optional[torch.Tensor] = None,
                 prefetch: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-                tp: Optional["C.TpHandoff"] = None, fold: int = 1) -> torch.Tensor:
+                tp: Optional["C.TpHandoff"] = None, fold: int = 1, kv_hint: Optional[tuple] = None) -> torch.Tensor:
     """y = epilogue(prologue(x) @ dequant(W).T) over tiled matrices; see b200_qgemv_tiled in include/b200gpt.h.
     ``tp``: tensor-parallel hand-off over peer memory (lit_gpt_b200/p2p.py builds it).  ``fold``: the tiled buffer is
     the (N / fold, fold * K) view of the flat 4-bit storage (shards whose K is not a multiple of the block)."""
@@ -288,12 +288,19 @@ def qgemv_tiled(x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, quant_type
     delta, residual, bias, bias2, norm_weight = (_bf16c(delta, "delta"), _bf16c(residual, "residual"), _bf16c(bias, "bias"),
                                                  _bf16c(bias2, "bias2"), _bf16c(norm_weight, "norm_weight"))
     ws = _ws("qgemv_tiled", x.device, C.load().b200_qgemv_tiled_workspace_bytes())
+    hint = None
+    if kv_hint is not None:  # (k_cache, v_cache, pos): L2 prefetch of the filled cache rows for the attention step that follows
+        kc, vc, pos = kv_hint
+        hint = C.KvHint(k=kc.data_ptr(), v=vc.data_ptr(), pos=pos.data_ptr(), pos_is_int64=int(pos.dtype == torch.int64),
+                        chunks=kc.shape[0] * kc.shape[1], chunk_stride=kc.shape[2] * kc.shape[3] * kc.element_size(),
+                        row_bytes=kc.shape[3] * kc.element_size(), max_rows=kc.shape[2])
     args = C.QGemvTiledArgs(
         tiled=tiled.data_ptr(), tiled2=C.ptr(tiled2), qtype=QTYPES[quant_type], blocksize=blocksize, N=N, K=K, x=x.data_ptr(),
         delta=C.ptr(delta), x_out=C.ptr(x_out), norm_weight=C.ptr(norm_weight), norm_eps=norm_eps, batch=batch, epilogue=epilogue,
         bias=C.ptr(bias), bias2=C.ptr(bias2), residual=C.ptr(residual), y=y.data_ptr(), prefetch=C.ptr(prefetch),
         prefetch_bytes=0 if prefetch is None else prefetch.numel() * prefetch.element_size(),
-        workspace=ws.data_ptr(), workspace_bytes=ws.numel(), tp=None if tp is None else ctypes.pointer(tp), fold=fold)
+        workspace=ws.data_ptr(), workspace_bytes=ws.numel(), tp=None if tp is None else ctypes.pointer(tp), fold=fold,
+        kv_hint=None if hint is None else ctypes.pointer(hint))
     C.check(C.load().b200_qgemv_tiled(ctypes.byref(args), C.stream_ptr(x.device)), "qgemv_tiled")
     return y
 

@@ -278,12 +278,13 @@ class GPT(nn.Module):
         for li, block in enumerate(blocks):
             a, m, cache = block.attn, block.mlp, block.attn.kv_cache
             nxt_qkv = blocks[li + 1].attn.attn if li + 1 < len(blocks) else self.lm_head
+            hint = (cache.k, cache.v, input_pos)  # L2 hint: the filled K / V rows this block's attention reads next
             if delta is not None:  # TP: the all-reduced branch output is added in the next prologue
                 x_new = torch.empty_like(x)
-                qkv = lin(a.attn, x, a.proj, delta=delta, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps)
+                qkv = lin(a.attn, x, a.proj, delta=delta, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps, kv_hint=hint)
                 x = x_new
             else:
-                qkv = lin(a.attn, x, a.proj, norm_weight=block.norm_1.weight, norm_eps=eps)
+                qkv = lin(a.attn, x, a.proj, norm_weight=block.norm_1.weight, norm_eps=eps, kv_hint=hint)
             y = K.attn_decode(qkv, self.cos, self.sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups,
                               c.head_size, c.rope_n_elem)
             if tp:

@@ -329,6 +329,7 @@ class QLinear(nn.Module):
         if other is not None:
             kw.update(packed2=other.weight.data, scale2=other.scale)
         kw.pop("bias2", None)
+        kw.pop("kv_hint", None)
         return K.qgemv(x, self.weight.data, self.scale, self.out_features, self.in_features, self.quant_type,
                        self.blocksize, **kw)
 
