@@ -149,6 +149,7 @@ int b200_p2p_free(void* ptr);
  * has been issued, the kernel asks the L2 for the filled part of this layer's K / V cache (cp.async.bulk.prefetch.L2), so that
  * the attention kernel's dependent loads hit L2 instead of HBM.  `chunks` = batch * n_query_groups contiguous (Tmax, hs) planes
  * per tensor, `chunk_stride` bytes apart; rows [0, *pos) of `row_bytes` each are fetched.  A hint only: no effect on results. */
+struct b200_attn_decode_args;
 typedef struct b200_kv_hint {
   const void* k;
   const void* v;
@@ -184,6 +185,13 @@ typedef struct b200_qgemv_tiled_args {
   size_t workspace_bytes;
   const struct b200_tp_handoff* tp; /* optional tensor-parallel hand-off (below); NULL on one GPU */
   const b200_kv_hint* kv_hint; /* optional (above); NULL = none */
+  const struct b200_attn_decode_args* attn; /* optional: the decode-attention step that consumes this launch's output, FUSED into
+                              the same kernel (replaces lit_gpt/model.py:619 + 624-653 with one launch): y is the interleaved QKV row,
+                              attn->qkv must equal y, attn->out receives (1, n_head * head_size).  Batch 1, n_head == n_query_groups,
+                              head size 128, STORE epilogue; each head's attention runs on the CTA of the same index as soon as the
+                              head's q / k / v rows are stored (per-head counters in the workspace), four key ranges on four
+                              128-thread sub-blocks merged in shared memory.  Anything else: B200_ERR_UNSUPPORTED, nothing launched
+                              (call b200_attn_decode separately).  attn->workspace is not used. */
   int fold;                /* 0 / 1: plain.  F = 2, 4: `tiled` holds the matrix VIEWED as (N / F, F * K), i.e. b200_tile_4bit(N / F, F * K)
                               of the same flat nf4 / fp4 buffers: for row-parallel shards whose K is not a multiple of the
                               64-element block while F * K is (generate/tp.py:28-45 cuts mlp.proj to 11008 / 8 = 1376 columns, and

@@ -53,7 +53,7 @@ class QGemvTiledArgs(ctypes.Structure):
         ("norm_eps", c_float), ("batch", c_int), ("epilogue", c_int),
         ("bias", c_void_p), ("bias2", c_void_p), ("residual", c_void_p), ("y", c_void_p),
         ("prefetch", c_void_p), ("prefetch_bytes", c_int64), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
-        ("tp", ctypes.POINTER(TpHandoff)), ("kv_hint", ctypes.POINTER(KvHint)), ("fold", c_int),
+        ("tp", ctypes.POINTER(TpHandoff)), ("kv_hint", ctypes.POINTER(KvHint)), ("attn", c_void_p), ("fold", c_int),
     ]
 
 

@@ -26,8 +26,12 @@ struct AttnParams {
   float* ws_ml;     // [batch][n_head][nsplit][2]
   unsigned int* ws_cnt;  // [batch][n_groups * head_chunks]
   float scale_log2;
+  unsigned int* fuse_cnt;   // fused into the QKV GEMV (qgemv_v4.cu): per-head row-tile counters, cleared by the merging sub-block
 };
 
+// validates `a` for the decode attention fused into the QKV GEMV (qgemv_v4.cu: batch 1, n_head == n_groups, head size 128,
+// splits as sub-blocks of one CTA) and fills the kernel parameters; B200_ERR_UNSUPPORTED (no message) when it does not apply
+int attn_fused_params(const b200_attn_decode_args* a, int nsplit, AttnParams* out);
 // grouped-query kernel on mma.sync (attn_decode_gqa.cu)
 bool attn_decode_gqa_supported(int head_size, int qpk);
 cudaError_t launch_attn_decode_gqa(const AttnParams& p, dim3 grid, cudaStream_t st);
@@ -81,9 +85,14 @@ __device__ __forceinline__ float ld_act_bf16(const __nv_bfloat16* p) {
 // CLUSTER: the nsplit CTAs of one (batch, group, head chunk) form a thread-block cluster (launch attribute); their split
 // partials stay in shared memory and cluster rank 0 merges them through distributed shared memory -- no workspace, no
 // fence, no ticket, three dependent L2 round trips fewer than the workspace protocol.
-template <int HS, int QPK, int DPL, typename Sync, bool CLUSTER = false>
+// INTRA: the nsplit (<= 4) splits of one item are 128-thread sub-blocks of ONE CTA (AttnSmem instances contiguous in shared
+// memory, `sm` being this sub-block's); `syncall()` is a barrier over all of them; sub-block 0 merges from shared memory.
+struct NoSync {
+  __device__ __forceinline__ void operator()() const {}
+};
+template <int HS, int QPK, int DPL, typename Sync, bool CLUSTER = false, bool INTRA = false, typename SyncAll = NoSync, int KPI_ = 4>
 __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<HS, QPK>& sm, const int tid, const int split, const int by,
-                                                 const int b, Sync sync) {
+                                                 const int b, Sync sync, SyncAll syncall = SyncAll{}) {
   constexpr int LPK = HS / DPL, GPW = 32 / LPK, SLOTS = 4 * GPW, NR = DPL / 2;
   float (&s_q)[QPK][HS] = sm.q;
   float (&s_k)[HS] = sm.k;
@@ -197,7 +206,7 @@ __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<H
   const int64_t kbeg = (int64_t)split * per, kend = min(pos, kbeg + per);
   const __nv_bfloat16* kbase = p.kc + ((int64_t)b * p.n_groups + gi) * p.max_seq * HS + dl * DPL;
   const __nv_bfloat16* vbase = p.vc + ((int64_t)b * p.n_groups + gi) * p.max_seq * HS + dl * DPL;
-  constexpr int KPI = 4;  // keys per lane group and iteration: all their K / V rows are in flight before the first update
+  constexpr int KPI = KPI_;  // keys per lane group and iteration: all their K / V rows are in flight before the first update
   for (int64_t base = kbeg + warp * GPW; base < kend; base += KPI * SLOTS) {  // warp-uniform trip count
     uint32_t kr[KPI][NR], vr[KPI][NR];
     bool ok[KPI];
@@ -259,11 +268,11 @@ __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<H
 #pragma unroll
       for (int w = 0; w < 4; ++w) a += s_acc[w][h][d] * c[w];
       if (p.nsplit == 1) p.out[((int64_t)b * H + head) * HS + d] = __float2bfloat16_rn(a / lt);
-      else if (CLUSTER) s_q[h][d] = a;   // q lives in registers by now: its shared-memory rows carry the split partial
+      else if (CLUSTER || INTRA) s_q[h][d] = a;   // q lives in registers by now: its shared-memory rows carry the split partial
       else __stcg(p.ws_acc + (((int64_t)b * H + head) * p.nsplit + split) * HS + d, a);
     }
     if (p.nsplit > 1 && tid == 0) {
-      if (CLUSTER) { sm.pm[h] = mn; sm.pl[h] = lt; }
+      if (CLUSTER || INTRA) { sm.pm[h] = mn; sm.pl[h] = lt; }
       else {
         float* ml = p.ws_ml + (((int64_t)b * H + head) * p.nsplit + split) * 2;
         __stcg(ml, mn);
@@ -271,7 +280,28 @@ __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<H
       }
     }
   }
-  if (p.nsplit == 1) return;
+  if (p.nsplit == 1) {
+    if (p.fuse_cnt && tid == 0) p.fuse_cnt[by] = 0u;
+    return;
+  }
+  if constexpr (INTRA) {
+    syncall();   // every sub-block's partial (m, l, o) is in shared memory
+    if (split == 0) {
+      const int NS = p.nsplit;
+      const AttnSmem<HS, QPK>* sib = &sm;   // sub-block r of this item: sib[r]
+      for (int i = tid; i < nh * HS; i += 128) {
+        const int h = i / HS, d = i % HS;
+        float mn = -INFINITY, lt = 0.f, a = 0.f;
+        for (int r = 0; r < NS; ++r) mn = fmaxf(mn, sib[r].pm[h]);
+        for (int r = 0; r < NS; ++r) lt += sib[r].pm[h] == -INFINITY ? 0.f : sib[r].pl[h] * exp2f(sib[r].pm[h] - mn);
+        const float inv = 1.f / lt;
+        for (int r = 0; r < NS; ++r) a = fmaf(sib[r].q[h][d], sib[r].pm[h] == -INFINITY ? 0.f : exp2f(sib[r].pm[h] - mn) * inv, a);
+        p.out[((int64_t)b * H + gi * p.qpk + h0 + h) * HS + d] = __float2bfloat16_rn(a);
+      }
+      if (p.fuse_cnt && tid == 0) p.fuse_cnt[by] = 0u;   // every sub-block is past its wait on the counter
+    }
+    return;
+  }
   if constexpr (CLUSTER) {
     // cluster barrier #1: every split's partial is in its CTA's shared memory
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -318,7 +348,7 @@ __device__ __forceinline__ void attn_decode_item(const AttnParams& p, AttnSmem<H
     unsigned int* cnt = p.ws_cnt + (int64_t)b * p.n_groups * p.head_chunks + by;
     const unsigned int old = atomicAdd(cnt, 1u);
     s_last = old == (unsigned int)(p.nsplit - 1);
-    if (s_last) *cnt = 0u;  // self-cleaning
+    if (s_last) { *cnt = 0u; if (p.fuse_cnt) p.fuse_cnt[by] = 0u; }  // self-cleaning
   }
   sync();
   if (!s_last) return;

@@ -185,6 +185,29 @@ int b200_attn_decode(const b200_attn_decode_args* a, b200_stream_t stream) {
   return B200_OK;
 }
 
+}  // extern "C"
+
+namespace b200 {
+int attn_fused_params(const b200_attn_decode_args* a, int nsplit, AttnParams* out) {
+  if (!a || !a->qkv || !a->cos || !a->sin || !a->pos || !a->k_cache || !a->v_cache || !a->out) return B200_ERR_UNSUPPORTED;
+  if (a->batch != 1 || a->n_head <= 0 || a->n_head != a->n_groups || a->head_size != 128 || a->max_seq <= 0) return B200_ERR_UNSUPPORTED;
+  if (a->rope_n_elem < 0 || a->rope_n_elem > a->head_size || a->rope_n_elem % 2) return B200_ERR_UNSUPPORTED;
+  if (a->table_dtype != B200_F32 && a->table_dtype != B200_BF16) return B200_ERR_UNSUPPORTED;
+  AttnParams p{};
+  p.qkv = (const __nv_bfloat16*)a->qkv;
+  p.cos = a->cos; p.sin = a->sin; p.table_bf16 = a->table_dtype == B200_BF16; p.table_presel = a->table_preselected; p.rope_n = a->rope_n_elem;
+  p.pos = a->pos; p.pos_i64 = a->pos_is_int64;
+  p.kc = (__nv_bfloat16*)a->k_cache; p.vc = (__nv_bfloat16*)a->v_cache; p.out = (__nv_bfloat16*)a->out;
+  p.batch = 1; p.n_head = a->n_head; p.n_groups = a->n_groups; p.hs = a->head_size; p.max_seq = a->max_seq; p.qpk = 1;
+  p.nsplit = nsplit; p.head_chunks = 1;
+  p.scale_log2 = (1.0f / sqrtf((float)a->head_size)) * 1.4426950408889634f;
+  *out = p;
+  return B200_OK;
+}
+}  // namespace b200
+
+extern "C" {
+
 // ---- allocation-free variant (no counterpart in the reference) ------------
 // Same kernel, same arguments, but the split-K scratch (partial (m, l, o) + ticket counters) lives in a file-scope
 // device array instead of a caller-provided workspace: for callers that cannot call cudaMalloc (CUDA graph capture,

@@ -641,6 +641,11 @@ static int qgemv_tiled_impl(const b200_qgemv_tiled_args* a, b200_stream_t stream
     set_error("b200_qgemv_tiled: batch %d x K %lld (fold %d) does not fit the stream-K kernel's shared memory plan", a->batch, (long long)a->K, fold);
     return B200_ERR_UNSUPPORTED;
   }
+  if (a->attn) {
+    set_error("b200_qgemv_tiled: the fused attention step needs batch 1, n_head == n_query_groups, head size 128, N = 3 * n_head * 128 >= 16 * SMs "
+              "and the STORE epilogue; call b200_attn_decode separately");
+    return B200_ERR_UNSUPPORTED;
+  }
 
   StreamParams p{};
   const bool swiglu = a->epilogue == B200_EPI_SWIGLU;

@@ -27,6 +27,7 @@
 // memory; for batch 1 the activation row lives in the unused halves of the 256 B table rows.
 #include "qgemv_v4.cuh"
 #include "stream_common.cuh"
+#include "attn_body.cuh"
 
 namespace b200 {
 
@@ -71,6 +72,8 @@ struct V4Params {
   uint32_t* tp_recv_done;
   const uint8_t* kvh_k; const uint8_t* kvh_v; const void* kvh_pos;   // K / V cache L2 hint (b200_kv_hint), kvh_k == NULL: none
   int kvh_i64, kvh_chunks, kvh_row, kvh_max; long long kvh_stride;
+  // fused decode attention (b200_qgemv_tiled_args::attn): parameters, 128-thread sub-blocks per head, row tiles per head, counters
+  AttnParams att; int att_nsplit, att_tph; unsigned int* att_cnt;
   int wu, nwin;     // k-windows (batch > 1 whose activation rows do not fit shared memory): units per tile and window, window count
   int fold;         // row folding (b200_qgemv_tiled_args::fold): N, K, batch above are the FOLDED view; outputs are unfolded
   int64_t Nout;     // true output features (fold * N)
@@ -140,7 +143,7 @@ __device__ __forceinline__ float ld_cg_f32(const float* p) {
 // MODE 0: batch 1 (one accumulator column), MODE 1: batch <= 8, MODE 2: batch <= 16
 // XREG (batch 1, units per tile == consumer warps): a warp meets the same k-range in every unit, so its activation
 // fragments (and int4 block sums) stay in registers for the whole launch instead of being re-read from shared memory
-template <int RU, bool INT4, int MODE, bool XREG, int OCC = 1, bool WIN = false>
+template <int RU, bool INT4, int MODE, bool XREG, int OCC = 1, bool WIN = false, bool ATT = false>
 __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Params p) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   constexpr int NB = MODE == 2 ? 2 : 1;
@@ -238,7 +241,7 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
         u += cnt;
         if (++ps == S) { ps = 0; pph ^= 1u; }
       }
-      if (p.debug != 3) v4_stamp(p, 6);
+      if (p.debug != 3 && !ATT) v4_stamp(p, 6);
       if (p.kvh_k) {
         // this launch's weight stream is issued: ask the L2 for the filled rows of the K / V cache the attention kernel reads
         // next (one plane per CTA).  pos may lag by one step here (no dependency wait on this path): it is only a hint
@@ -350,7 +353,7 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
       if (lane == 0) v4_stamp(p, 5);
       return;
     }
-    if (lane == 0 && p.debug != 3) v4_stamp(p, 7);
+    if (lane == 0 && p.debug != 3 && !ATT) v4_stamp(p, 7);
     int j = 0;  // tiles reduced so far (reduction-buffer sequence)
     for (int e = e_first; e <= e_last; ++e) {
       float val[2][NV];
@@ -434,6 +437,20 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
         }
       }
       finish(e, val);
+    }
+    if constexpr (ATT) {
+      // this CTA's row tiles of q / k / v are in memory: tell the attention sub-blocks, ONE fence for all of them (a fence
+      // per tile cost ~0.6 us each); the tiles of a CTA span at most a few heads
+      __threadfence();
+      __syncwarp();
+      if (lane == 0) {
+        int e = e_first;
+        while (e <= e_last) {
+          const int h = e / p.att_tph, e_end = min(e_last + 1, (h + 1) * p.att_tph);
+          asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p.att_cnt + h), "r"((uint32_t)(e_end - e)) : "memory");
+          e = e_end;
+        }
+      }
     }
     if (lane == 0) v4_stamp(p, 5);
     return;
@@ -1010,6 +1027,34 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
   }
   while (ct <= t_last) flush();
   if (tid == 0 && p.debug != 3) v4_stamp(p, 4);
+  if constexpr (ATT) {
+    // ---- fused decode attention: head `cta` on this CTA, att_nsplit key ranges on 128-thread sub-blocks ---------------
+    asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");   // every consumer warp is done with the ring: reuse it
+    const int sub = warp >> 2;
+    if (cta < p.att.n_head && sub < p.att_nsplit) {
+      const int t128 = tid & 127;
+      if (t128 == 0) {   // the head's q, k and v rows (att_tph row tiles, stored by up to a few CTAs' reducers)
+        const long long t0 = clock64();
+        while (ld_acquire_gpu(p.att_cnt + cta) < (uint32_t)p.att_tph) {
+          if (clock64() - t0 > 4000000000LL) { *reinterpret_cast<volatile uint32_t*>(p.ws) = 3u; break; }   // error word, no hang
+        }
+      }
+      struct SubSync {
+        int id;
+        __device__ __forceinline__ void operator()() const { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
+      };
+      struct AllSync {
+        int n;
+        __device__ __forceinline__ void operator()() const { asm volatile("bar.sync 6, %0;" ::"r"(n) : "memory"); }
+      };
+      const SubSync ssync{2 + sub};
+      ssync();
+      AttnSmem<128, 1>* smA = reinterpret_cast<AttnSmem<128, 1>*>(sb + pl.ringA);
+      if (t128 == 0 && sub == 0) v4_stamp(p, 6);   // trace: counter wait over
+      attn_decode_item<128, 1, 16, SubSync, false, true, AllSync, 2>(p.att, smA[sub], t128, sub, cta, 0, ssync, AllSync{p.att_nsplit * 128});
+      if (t128 == 0 && sub == 0) v4_stamp(p, 7);   // trace: attention done
+    }
+  }
 }
 
 static unsigned long long* g_v4_trace = nullptr;   // development: device buffer [slots][kV4MaxCtas][8]
@@ -1057,9 +1102,25 @@ static cudaError_t launch_v4_win(const V4Params& p, int gx, cudaStream_t st) {
   return launch(qgemv_v4_kernel<RU, INT4, MODE, false, 1, true>, dim3(gx), dim3(kV4Threads), (size_t)kV4DynSmem, st, p);
 }
 
+template <int RU, bool INT4, bool XREG>
+static cudaError_t launch_v4_att(const V4Params& p, int gx, cudaStream_t st) {
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(qgemv_v4_kernel<RU, INT4, 0, XREG, 1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kV4DynSmem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  return launch(qgemv_v4_kernel<RU, INT4, 0, XREG, 1, false, true>, dim3(gx), dim3(kV4Threads), (size_t)kV4DynSmem, st, p);
+}
+
 template <bool INT4, int MODE>
 static cudaError_t launch_v4_ru(int ru, const V4Params& p, int gx, cudaStream_t st) {
   constexpr int RUMAX = INT4 ? 2 : 4;
+  if constexpr (MODE == 0) {
+    if (p.att_nsplit > 0) {   // the host checked ru == RUMAX
+      return (p.upt == kV4CW && g_v4_xreg.load()) ? launch_v4_att<RUMAX, INT4, true>(p, gx, st) : launch_v4_att<RUMAX, INT4, false>(p, gx, st);
+    }
+  }
   if constexpr (MODE != 0) {
     if (p.nwin > 1) return ru == RUMAX ? launch_v4_win<RUMAX, INT4, MODE>(p, gx, st) : launch_v4_win<1, INT4, MODE>(p, gx, st);
   }
@@ -1133,6 +1194,19 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
   if (ru == 0) return B200_ERR_UNSUPPORTED;
   const int64_t U = ntiles * ts * (nrec / ru);
   if (U <= 0 || U > 0x3fffffff) return B200_ERR_UNSUPPORTED;
+  // fused decode attention: batch 1, whole row tiles per head, one CTA per head
+  AttnParams att{};
+  int att_nsplit = 0, att_tph = 0;
+  if (a0->attn) {
+    const b200_attn_decode_args* at = a0->attn;
+    int sms = sm_count();
+    if (sms > kV4MaxCtas) sms = kV4MaxCtas;
+    if (fold != 1 || mode != 0 || swiglu || a0->epilogue != B200_EPI_STORE || a0->tp || nwin > 1 || ru != (int4 ? 2 : 4) ||
+        (!dry && (at->qkv != a0->y || !a0->y)) || at->n_head > sms || ntiles < sms ||
+        a0->N != (int64_t)3 * at->n_head * at->head_size || attn_fused_params(at, 4, &att) != B200_OK)
+      return B200_ERR_UNSUPPORTED;
+    att_nsplit = 4; att_tph = 3 * at->head_size / 16;
+  }
   if (dry) return B200_OK;
 
   V4Params p{};
@@ -1151,6 +1225,8 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
   p.y = reinterpret_cast<__nv_bfloat16*>(a->y);
   p.xstride = xstride; p.gap = gap;
   p.wu = wu; p.nwin = nwin;
+  p.att = att; p.att_nsplit = att_nsplit; p.att_tph = att_tph;
+  if (att_nsplit) { p.att_cnt = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(a->workspace) + 1024); p.att.fuse_cnt = p.att_cnt; }
   if (nwin > 1) { p.nkb = win_nkb; p.xstride = win_xstride; }
   p.fold = fold; p.Nout = a0->N; p.Kin = (int)a0->K;
   if (a0->kv_hint && a0->kv_hint->k && a0->kv_hint->v && a0->kv_hint->pos && g_v4_kvhint.load()) {
@@ -1180,7 +1256,7 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
   // (~2 us exposed: fence + flag + two L2 round trips): bytes of imbalance at ~6 TB/s.
   const int64_t E = ntiles;                       // entities (tiles, or gate/up pairs)
   const int64_t ent_bytes = (int64_t)ts * nrec * (int4 ? 1088 : 576);
-  const int force = nwin > 1 ? 0 : g_v4_split.load();   // k-windows keep whole entities per CTA
+  const int force = (nwin > 1 || att_nsplit) ? 0 : g_v4_split.load();   // k-windows and the fused attention keep whole entities per CTA
   if (E >= gx) {
     const double waste_us = (double)(((E + gx - 1) / gx) * gx - E) / gx * ent_bytes / 6.0e6;   // idle share of the last wave
     p.split = force >= 0 ? force : (waste_us > 2.5 ? 1 : 0);

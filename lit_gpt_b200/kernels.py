@@ -273,7 +273,8 @@ def qgemv_tiled(x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, quant_type
                 x_out: Optional[torch.Tensor] = None, norm_weight: Optional[torch.Tensor] = None, norm_eps: float = 1e-5,
                 residual: Optional[torch.Tensor] = None, tiled2: Optional[torch.Tensor] = None,
                 prefetch: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-                tp: Optional["C.TpHandoff"] = None, fold: int = 1, kv_hint: Optional[tuple] = None) -> torch.Tensor:
+                tp: Optional["C.TpHandoff"] = None, fold: int = 1, kv_hint: Optional[tuple] = None,
+                attn: Optional[dict] = None) -> torch.Tensor:
     """y = epilogue(prologue(x) @ dequant(W).T) over tiled matrices; see b200_qgemv_tiled in include/b200gpt.h.
     ``tp``: tensor-parallel hand-off over peer memory (lit_gpt_b200/p2p.py builds it).  ``fold``: the tiled buffer is
     the (N / fold, fold * K) view of the flat 4-bit storage (shards whose K is not a multiple of the block)."""
@@ -294,15 +295,34 @@ def qgemv_tiled(x: torch.Tensor, tiled: torch.Tensor, N: int, K: int, quant_type
         hint = C.KvHint(k=kc.data_ptr(), v=vc.data_ptr(), pos=pos.data_ptr(), pos_is_int64=int(pos.dtype == torch.int64),
                         chunks=kc.shape[0] * kc.shape[1], chunk_stride=kc.shape[2] * kc.shape[3] * kc.element_size(),
                         row_bytes=kc.shape[3] * kc.element_size(), max_rows=kc.shape[2])
+    at = None
+    if attn is not None:  # the decode-attention step fused into this (QKV) launch: y is its input, attn["out"] its output
+        kc, vc, pos, cos, sin = attn["k_cache"], attn["v_cache"], attn["pos"], attn["cos"], attn["sin"]
+        at = C.AttnDecodeArgs(
+            qkv=y.data_ptr(), cos=cos.data_ptr(), sin=sin.data_ptr(), table_dtype=_table_code(cos), table_preselected=0,
+            rope_n_elem=attn["rope_n_elem"], pos=pos.data_ptr(), pos_is_int64=int(pos.dtype == torch.int64), k_cache=kc.data_ptr(),
+            v_cache=vc.data_ptr(), out=attn["out"].data_ptr(), batch=kc.shape[0], n_head=attn["n_head"], n_groups=attn["n_groups"],
+            head_size=attn["head_size"], max_seq=kc.shape[2], num_splits=0, workspace=None, workspace_bytes=0)
     args = C.QGemvTiledArgs(
         tiled=tiled.data_ptr(), tiled2=C.ptr(tiled2), qtype=QTYPES[quant_type], blocksize=blocksize, N=N, K=K, x=x.data_ptr(),
         delta=C.ptr(delta), x_out=C.ptr(x_out), norm_weight=C.ptr(norm_weight), norm_eps=norm_eps, batch=batch, epilogue=epilogue,
         bias=C.ptr(bias), bias2=C.ptr(bias2), residual=C.ptr(residual), y=y.data_ptr(), prefetch=C.ptr(prefetch),
         prefetch_bytes=0 if prefetch is None else prefetch.numel() * prefetch.element_size(),
         workspace=ws.data_ptr(), workspace_bytes=ws.numel(), tp=None if tp is None else ctypes.pointer(tp), fold=fold,
-        kv_hint=None if hint is None else ctypes.pointer(hint))
+        kv_hint=None if hint is None else ctypes.pointer(hint), attn=None if at is None else ctypes.addressof(at))
     C.check(C.load().b200_qgemv_tiled(ctypes.byref(args), C.stream_ptr(x.device)), "qgemv_tiled")
     return y
+
+
+@functools.lru_cache(maxsize=None)
+def qgemv_attn_fusable(N: int, K: int, quant_type: str, n_head: int, n_groups: int, head_size: int, rope_n_elem: int, max_seq: int) -> bool:
+    """Whether b200_qgemv_tiled can run the decode attention of (n_head, n_groups, head_size) fused into the QKV GEMV (dry run)."""
+    at = C.AttnDecodeArgs(qkv=256, cos=256, sin=256, table_dtype=0, table_preselected=0, rope_n_elem=rope_n_elem, pos=256,
+                          pos_is_int64=1, k_cache=256, v_cache=256, out=256, batch=1, n_head=n_head, n_groups=n_groups,
+                          head_size=head_size, max_seq=max_seq, num_splits=0, workspace=None, workspace_bytes=0)
+    args = C.QGemvTiledArgs(qtype=QTYPES[quant_type], blocksize=128 if quant_type == "int4" else 64, N=N, K=K, batch=1,
+                            epilogue=C.EPI_STORE, attn=ctypes.addressof(at))
+    return bool(C.load().b200_qgemv_tiled_supported(ctypes.byref(args)))
 
 
 @functools.lru_cache(maxsize=None)

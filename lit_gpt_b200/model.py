@@ -275,18 +275,37 @@ class GPT(nn.Module):
             else:
                 logits = lin(self.lm_head, x, delta=pending, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
             return logits.view(B, 1, -1)
+        import os
+
+        a0 = blocks[0].attn.attn if blocks else None
+        # EXPERIMENT, off by default (B200_FUSE_ATTN_MAX_SEQ=1024 enables it): the attention step fused into the QKV GEMV's
+        # kernel (b200_qgemv_tiled_args::attn).  Correct (tests/test_gpu_kernels.py::test_qgemv_tiled_fused_attention) and 32
+        # launches per token fewer, but measured SLOWER on B200 (632 vs 676 tok/s): in-kernel the
+        # attention tail runs on one SM per head at the GEMV's register budget, 5.5 - 7.5 us against ~6 us for the stand-alone
+        # cluster kernel INCLUDING its launch boundary
+        fuse_attn = (not tp and B == 1 and a0 is not None and self.max_seq_length <= int(os.environ.get("B200_FUSE_ATTN_MAX_SEQ", "0"))
+                     and a0.fold == 1 and a0.streams(1) and input_pos.numel() == 1
+                     and K.qgemv_attn_fusable(a0.out_features, a0.in_features, a0.quant_type, c.n_head, c.n_query_groups, c.head_size,
+                                              c.rope_n_elem, self.max_seq_length))
         for li, block in enumerate(blocks):
             a, m, cache = block.attn, block.mlp, block.attn.kv_cache
             nxt_qkv = blocks[li + 1].attn.attn if li + 1 < len(blocks) else self.lm_head
             hint = (cache.k, cache.v, input_pos)  # L2 hint: the filled K / V rows this block's attention reads next
-            if delta is not None:  # TP: the all-reduced branch output is added in the next prologue
+            if fuse_attn:
+                # the attention step runs inside the QKV GEMV's kernel (b200_qgemv_tiled_args::attn): one launch boundary less
+                y = torch.empty((B, c.n_head * c.head_size), dtype=torch.bfloat16, device=x.device)
+                qkv = lin(a.attn, x, a.proj, norm_weight=block.norm_1.weight, norm_eps=eps, kv_hint=hint,
+                          attn=dict(k_cache=cache.k, v_cache=cache.v, pos=input_pos, cos=self.cos, sin=self.sin, out=y, n_head=c.n_head,
+                                    n_groups=c.n_query_groups, head_size=c.head_size, rope_n_elem=c.rope_n_elem))
+            elif delta is not None:  # TP: the all-reduced branch output is added in the next prologue
                 x_new = torch.empty_like(x)
                 qkv = lin(a.attn, x, a.proj, delta=delta, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps, kv_hint=hint)
                 x = x_new
             else:
                 qkv = lin(a.attn, x, a.proj, norm_weight=block.norm_1.weight, norm_eps=eps, kv_hint=hint)
-            y = K.attn_decode(qkv, self.cos, self.sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups,
-                              c.head_size, c.rope_n_elem)
+            if not fuse_attn:
+                y = K.attn_decode(qkv, self.cos, self.sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups,
+                                  c.head_size, c.rope_n_elem)
             if tp:
                 h = self._all_reduce(lin(a.proj, y, m.fc_1))
                 x_new = torch.empty_like(x)

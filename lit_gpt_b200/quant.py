@@ -330,6 +330,8 @@ class QLinear(nn.Module):
             kw.update(packed2=other.weight.data, scale2=other.scale)
         kw.pop("bias2", None)
         kw.pop("kv_hint", None)
+        if kw.pop("attn", None) is not None:
+            raise B200Error("QLinear.gemv: the fused attention step needs the streaming kernel (ask K.qgemv_attn_fusable first)")
         return K.qgemv(x, self.weight.data, self.scale, self.out_features, self.in_features, self.quant_type,
                        self.blocksize, **kw)
 

@@ -125,6 +125,43 @@ def test_qgemv_tuning_variants_agree(K, ks, occ):
     _check_gemv(y, x.float(), deq)
 
 
+@pytest.mark.parametrize("qt,H,Kdim", [("nf4", 32, 4096), ("int4", 40, 5120)])
+@pytest.mark.parametrize("pos", [0, 5, 271, 700])
+def test_qgemv_tiled_fused_attention(K, qt, H, Kdim, pos):
+    """The decode-attention step fused into the QKV GEMV (b200_qgemv_tiled_args::attn; lit_gpt/model.py:619 + 624-653 in one
+    launch) against the two separate launches: identical QKV row and cache append, attention output equal up to the order in
+    which the key ranges are merged (fp32 merge, bf16 output: 2^-7 relative)."""
+    hs, max_seq = 128, 1024
+    N = 3 * H * hs
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, 1, qt, seed=H + pos)
+    tiled = K.tile_4bit(packed, scale, N, Kdim, qt, bs)
+    assert K.qgemv_attn_fusable(N, Kdim, qt, H, H, hs, hs, max_seq)
+    g = torch.Generator().manual_seed(pos)
+    kc0 = torch.randn(1, H, max_seq, hs, generator=g).bfloat16().cuda()
+    vc0 = torch.randn(1, H, max_seq, hs, generator=g).bfloat16().cuda()
+    cos, sin = M.build_rope_cache(max_seq, hs)
+    cos, sin = cos.cuda(), sin.cuda()
+    nw = torch.ones(Kdim, dtype=torch.bfloat16, device="cuda")
+    p = torch.tensor([pos], device="cuda")
+    xs = (x * 40).cuda()   # spread the logits so that the softmax is not flat
+    # separate launches
+    kc1, vc1 = kc0.clone(), vc0.clone()
+    qkv1 = K.qgemv_tiled(xs, tiled, N, Kdim, qt, bs, norm_weight=nw, norm_eps=1e-5)
+    y1 = K.attn_decode(qkv1, cos, sin, p, kc1, vc1, H, H, hs, hs)
+    # fused
+    for rep in range(2):   # twice: the per-head counters must be left clean
+        kc2, vc2 = kc0.clone(), vc0.clone()
+        y2 = torch.full((1, H * hs), float("nan"), dtype=torch.bfloat16, device="cuda")
+        qkv2 = K.qgemv_tiled(xs, tiled, N, Kdim, qt, bs, norm_weight=nw, norm_eps=1e-5,
+                             attn=dict(k_cache=kc2, v_cache=vc2, pos=p, cos=cos, sin=sin, out=y2, n_head=H, n_groups=H, head_size=hs, rope_n_elem=hs))
+        torch.cuda.synchronize()
+        assert torch.equal(qkv1, qkv2)
+        assert torch.equal(kc1, kc2) and torch.equal(vc1, vc2)
+        assert torch.isfinite(y2.float()).all()
+        assert (y1.float() - y2.float()).abs().max() <= 2 ** -7 * y1.float().abs().max(), (y1.float() - y2.float()).abs().max()
+    K.check_gemv_errors(torch.device("cuda", 0))
+
+
 @pytest.mark.parametrize("qt", ["nf4", "int4"])
 @pytest.mark.parametrize("N,Kdim,B", [(5120, 13824, 16), (2048, 13824, 8), (1000, 5120, 16), (640, 8192, 16), (5120, 13824, 9), (96, 28672, 16)])
 def test_qgemv_tiled_k_windows(K, qt, N, Kdim, B):

@@ -83,8 +83,10 @@ def main() -> None:
         mx = lambda k: r[:, k][a[:, k] > 0].max() if (a[:, k] > 0).any() else float("nan")
         name = names[s % 4] if s < slots - 1 else "lm_head"
         gap = "" if prev_end is None else f"{t0 - prev_end:7.0f}"
-        print(f"{s:3d} {name:7s} {int(used.sum()):4d} | {med(0):6.0f} {mx(0):6.0f} | {med(1):6.0f} | {med(2):6.0f} | {med(3):6.0f} | {med(6):6.0f} | {med(4):6.0f} | {med(5):6.0f} {mx(5):6.0f} | {mx(5):6.0f} | prev-end->entry {gap}")
-        prev_end = a[:, 5][a[:, 5] > 0].max()
+        end = max(mx(5), mx(7)) if (a[:, 7] > 0).any() and name == "qkv" else mx(5)
+        extra = f" | fused attention: counters ready med {med(6):6.0f}, done med {med(7):6.0f} max {mx(7):6.0f}" if name == "qkv" and (a[:, 7] > 0).any() and med(7) > med(5) else ""
+        print(f"{s:3d} {name:7s} {int(used.sum()):4d} | {med(0):6.0f} {mx(0):6.0f} | {med(1):6.0f} | {med(2):6.0f} | {med(3):6.0f} | {med(6):6.0f} | {med(4):6.0f} | {med(5):6.0f} {mx(5):6.0f} | {end:6.0f} | prev-end->entry {gap}{extra}")
+        prev_end = max(a[:, 5][a[:, 5] > 0].max(), a[:, 7].max() if name == "qkv" and (a[:, 7] > a[:, 5]).any() else 0)
 
 
 if __name__ == "__main__":
