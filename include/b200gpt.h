@@ -132,7 +132,11 @@ int b200_untile_4bit(const void* tiled, int64_t N, int64_t K, int qtype, int blo
 typedef struct b200_tp_handoff {
   int world, rank;
   void* peer_y[8];        /* producer: slot `rank` (batch, N) uint32 packets in the buffer of rank r, own rank included */
-  void* reserved[8];      /* must be NULL */
+  void* reduced;          /* consumer, optional: LOCAL buffer of >= batch * K uint32 packets.  When set the exchange is summed in two
+                             stages: every CTA adds the `world` slots for ITS slice of the vector only and republishes the sums here as
+                             packets with the same tag, then all CTAs read this one buffer: world x fewer L2 reads per CTA (at world 8
+                             each CTA otherwise reads 8 x K x 4 bytes), one more local round trip.  Same arithmetic, bit-identical. */
+  void* reserved[7];      /* must be NULL */
   void* send_seq;         /* producer: LOCAL sequence counter of the buffer written; NULL = this launch is not a producer */
   const void* slots;      /* consumer: local slots, rank r at slots + r * slot_stride bytes; NULL = not a consumer */
   int64_t slot_stride;    /* >= batch * K * 4 bytes */

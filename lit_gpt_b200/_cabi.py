@@ -37,7 +37,7 @@ class QGemvArgs(ctypes.Structure):
 
 
 class TpHandoff(ctypes.Structure):  # mirrors b200_tp_handoff
-    _fields_ = [("world", c_int), ("rank", c_int), ("peer_y", c_void_p * 8), ("reserved", c_void_p * 8), ("send_seq", c_void_p),
+    _fields_ = [("world", c_int), ("rank", c_int), ("peer_y", c_void_p * 8), ("reduced", c_void_p), ("reserved", c_void_p * 7), ("send_seq", c_void_p),
                 ("slots", c_void_p), ("slot_stride", c_int64), ("recv_seq", c_void_p), ("recv_done", c_void_p)]
 
 

@@ -67,6 +67,7 @@ struct V4Params {
   uint32_t* tp_peer_y[8];
   const uint32_t* tp_send_seq;
   const uint32_t* tp_slots;
+  uint32_t* tp_reduced;      // two-stage exchange: local republish buffer (b200_tp_handoff::reduced), NULL = one stage
   int64_t tp_slot_stride;
   uint32_t* tp_recv_seq;
   uint32_t* tp_recv_done;
@@ -705,7 +706,42 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
           }
         }
       }
-    } else
+    } else {
+    const uint32_t* tp_src = p.tp_slots;
+    int tp_nw = p.tp_world;
+    if (p.tp_slots && p.tp_reduced) {
+      // two-stage exchange, stage 1: this CTA sums ITS slice of the vector over the ranks (fp32, rank order, one rounding to
+      // bf16: the arithmetic of the one-stage path) and republishes it locally as packets with the same tag; stage 2 below
+      // then reads one buffer instead of `world` slots
+      const int total = B * chunks;
+      const int i0 = (int)(((int64_t)total * cta) / G), i1 = (int)(((int64_t)total * (cta + 1)) / G);
+      for (int i = i0 + tid; i < i1; i += kV4Consumers) {
+        float acc8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int r = 0; r < p.tp_world; ++r) {
+          const uint32_t* sp = p.tp_slots + r * p.tp_slot_stride + (int64_t)i * 8;
+          uint4 pa, pb;
+          const long long t0 = clock64();
+          for (;;) {
+            asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(pa.x), "=r"(pa.y), "=r"(pa.z), "=r"(pa.w) : "l"(sp) : "memory");
+            asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(pb.x), "=r"(pb.y), "=r"(pb.z), "=r"(pb.w) : "l"(sp + 4) : "memory");
+            const bool ok = (pa.x >> 16) == rtag && (pa.y >> 16) == rtag && (pa.z >> 16) == rtag && (pa.w >> 16) == rtag &&
+                            (pb.x >> 16) == rtag && (pb.y >> 16) == rtag && (pb.z >> 16) == rtag && (pb.w >> 16) == rtag;
+            if (ok) break;
+            if (clock64() - t0 > 4000000000LL) { *reinterpret_cast<volatile uint32_t*>(p.ws) = 2u; break; }
+          }
+          acc8[0] += bf16lo(pa.x); acc8[1] += bf16lo(pa.y); acc8[2] += bf16lo(pa.z); acc8[3] += bf16lo(pa.w);
+          acc8[4] += bf16lo(pb.x); acc8[5] += bf16lo(pb.y); acc8[6] += bf16lo(pb.z); acc8[7] += bf16lo(pb.w);
+        }
+        const uint32_t tg = rtag << 16;
+        uint32_t* dp = p.tp_reduced + (int64_t)i * 8;
+        asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dp), "r"(tg | bf16_bits(acc8[0])), "r"(tg | bf16_bits(acc8[1])),
+                     "r"(tg | bf16_bits(acc8[2])), "r"(tg | bf16_bits(acc8[3])) : "memory");
+        asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dp + 4), "r"(tg | bf16_bits(acc8[4])), "r"(tg | bf16_bits(acc8[5])),
+                     "r"(tg | bf16_bits(acc8[6])), "r"(tg | bf16_bits(acc8[7])) : "memory");
+      }
+      tp_src = p.tp_reduced;
+      tp_nw = 1;
+    }
     for (int b = 0; b < B; ++b) {
       float ss = 0.f;
       for (int c = tid; c < chunks; c += kV4Consumers) {
@@ -720,8 +756,8 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
           uint4 dv;
           if (p.tp_slots) {  // sum of the ranks' partials in rank order (fp32), rounded once to bf16 like an all-reduced tensor
             float acc8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            for (int r = 0; r < p.tp_world; ++r) {
-              const uint32_t* sp = p.tp_slots + r * p.tp_slot_stride + (int64_t)b * p.K + c * 8;
+            for (int r = 0; r < tp_nw; ++r) {
+              const uint32_t* sp = tp_src + r * p.tp_slot_stride + (int64_t)b * p.K + c * 8;
               uint4 pa, pb;
               const long long t0 = clock64();
               for (;;) {   // poll until all eight packets carry this hand-off's tag
@@ -757,6 +793,7 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
         ss = warp_sum(ss);
         if (lane == 0) s_ssq[warp * 16 + b] = ss;
       }
+    }
     }
     if (tid == 0 && p.debug == 3) v4_stamp_cyc(p, 3, c_rel);
     if (p.norm_w) {
@@ -1247,6 +1284,7 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
       p.tp_slot_stride = h->slot_stride / 4;
       p.tp_recv_seq = reinterpret_cast<uint32_t*>(h->recv_seq);
       p.tp_recv_done = reinterpret_cast<uint32_t*>(h->recv_done);
+      p.tp_reduced = reinterpret_cast<uint32_t*>(h->reduced);
     }
   }
   if (g_v4_trace && g_v4_trace_next < g_v4_trace_slots) p.trace = g_v4_trace + (size_t)(g_v4_trace_next++) * kV4MaxCtas * 8;

@@ -37,7 +37,14 @@ class PeerComm:
         self.device = device
         self.slot_bytes = (int(slot_bytes) + 255) & ~255
         self.data_bytes = 2 * self.world * self.slot_bytes
-        total = self.data_bytes + 2 * FLAG_BLOCK
+        # two-stage exchange (b200_tp_handoff::reduced): every consumer CTA sums only its slice of the vector over the ranks and
+        # republishes it in a local buffer that all CTAs then read.  OFF by default: bit-identical, but the extra dependent round
+        # trip costs more than the world x fewer L2 reads save (TP-8 Llama-2-7B 703 vs 851 tok/s, 70B 205 vs 214).
+        # B200_TP_TWO_STAGE_MIN=<world> switches it on from that many ranks.
+        import os
+
+        self.two_stage = self.world >= int(os.environ.get("B200_TP_TWO_STAGE_MIN", "99"))
+        total = self.data_bytes + 2 * FLAG_BLOCK + 2 * self.slot_bytes
         lib = C.load()
         self._local, self._opened, self.base = 0, [], []
         # every stage is followed by a collective agreement, so that a failure on one rank fails all of them the same way
@@ -96,6 +103,8 @@ class PeerComm:
             h.slot_stride = self.slot_bytes
             h.recv_seq = self._flags(self._local, recv)
             h.recv_done = self._flags(self._local, recv) + 32
+            if self.two_stage:
+                h.reduced = self._local + self.data_bytes + 2 * FLAG_BLOCK + recv * self.slot_bytes
         return h
 
     def close(self) -> None:
