@@ -286,6 +286,9 @@ int b200_attn_prefill(const void* q, const void* k_cache, const void* v_cache, c
 
 /* ---- small glue kernels so a whole decode step is one CUDA graph of this library's kernels ---------------- */
 /* out[r, :] = wte[idx[r], :]  (lit_gpt/model.py:515) */
+/* y = silu(a) * b over n bf16 elements (replaces `F.silu(x_fc_1) * x_fc_2`, lit_gpt/model.py:715, on the prefill path; the decode GEMV
+ * has it as its SWIGLU epilogue).  Same rounding points as the reference's two ATen kernels: silu to bf16, product to bf16. */
+int b200_swiglu(const void* a, const void* b, void* y, int64_t n, b200_stream_t stream);
 int b200_embedding(const void* idx, int idx_is_int64, const void* wte, void* out, int64_t rows, int64_t dim,
                    int64_t vocab, b200_stream_t stream);
 /* greedy sampling: token[b] = argmax(logits[b, :vocab]) (generate/base.py:41).  If pos_inout != NULL: pos += 1

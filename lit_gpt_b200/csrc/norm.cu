@@ -44,6 +44,26 @@ __global__ void __launch_bounds__(256) rmsnorm_kernel(const __nv_bfloat16* __res
   }
 }
 
+// y = silu(a) * b elementwise over bf16 (lit_gpt/model.py:715 at prefill; the decode GEMV has it as its epilogue): the reference's
+// rounding points -- F.silu rounds to bf16, the product rounds to bf16 -- eight elements per thread and step
+__global__ void __launch_bounds__(256) swiglu_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
+                                                     __nv_bfloat16* __restrict__ y, int64_t n8) {
+  griddep_launch();
+  griddep_wait();
+  for (int64_t i = blockIdx.x * 256 + threadIdx.x; i < n8; i += (int64_t)gridDim.x * 256) {
+    const uint4 av = reinterpret_cast<const uint4*>(a)[i], bv = reinterpret_cast<const uint4*>(b)[i];
+    const uint32_t aw[4] = {av.x, av.y, av.z, av.w}, bw[4] = {bv.x, bv.y, bv.z, bv.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float a0 = bf16lo(aw[j]), a1 = bf16hi(aw[j]);
+      const float s0 = round_bf16(a0 / (1.0f + expf(-a0))), s1 = round_bf16(a1 / (1.0f + expf(-a1)));
+      o[j] = pack_bf16(s0 * bf16lo(bw[j]), s1 * bf16hi(bw[j]));
+    }
+    reinterpret_cast<uint4*>(y)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 template <typename IdxT>
 __global__ void __launch_bounds__(256) embedding_kernel(const IdxT* __restrict__ idx, const __nv_bfloat16* __restrict__ wte,
                                                         __nv_bfloat16* __restrict__ out, int64_t dim, int64_t vocab) {
@@ -120,6 +140,17 @@ int b200_rmsnorm(const void* x, const void* delta, const void* weight, float eps
   B200_CHECK_ARG(rows <= 0x7fffffff, "b200_rmsnorm: too many rows");
   B200_CUDA(launch(rmsnorm_kernel, dim3((unsigned)rows), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)x,
                    (const __nv_bfloat16*)delta, (const __nv_bfloat16*)weight, eps, (__nv_bfloat16*)y, (__nv_bfloat16*)sum_out, dim));
+  return B200_OK;
+}
+
+int b200_swiglu(const void* a, const void* b, void* y, int64_t n, b200_stream_t stream) {
+  B200_CHECK_ARG(a && b && y && n > 0 && n % 8 == 0, "b200_swiglu: null pointer or element count not a multiple of 8");
+  B200_CHECK_ARG(((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(y)) & 15) == 0, "b200_swiglu: pointers must be 16-byte aligned");
+  const int64_t n8 = n / 8;
+  int64_t blocks = (n8 + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  B200_CUDA(launch(swiglu_kernel, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)a, (const __nv_bfloat16*)b, (__nv_bfloat16*)y, n8));
   return B200_OK;
 }
 

@@ -392,6 +392,17 @@ def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float = 1e-5, delta: Opt
     return y
 
 
+def swiglu(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """silu(a) * b with the reference's bf16 rounding points (model.py:715), one kernel."""
+    C.require_cuda(a, b)
+    a, b = _bf16c(a, "a"), _bf16c(b, "b")
+    if a.shape != b.shape:
+        raise C.B200Error("swiglu: shape mismatch")
+    y = torch.empty_like(a)
+    C.check(C.load().b200_swiglu(a.data_ptr(), b.data_ptr(), y.data_ptr(), a.numel(), C.stream_ptr(a.device)), "swiglu")
+    return y
+
+
 def embedding(idx: torch.Tensor, wte: torch.Tensor) -> torch.Tensor:
     C.require_cuda(idx, wte)
     wte = _bf16c(wte, "wte")

@@ -88,6 +88,9 @@ class GPT(nn.Module):
             # (a traced forward takes the module path: its kernels are registered custom ops, the fused chain is raw C-ABI calls)
             if T == 1 and input_pos.numel() == 1 and not torch.compiler.is_compiling() and self.fused_decode_ready(idx):
                 return self._fused_decode(idx, input_pos)
+            if (T > 1 and input_pos.numel() == T and input_pos.is_cuda and not torch.compiler.is_compiling() and self.fused_decode_ready(idx)
+                    and self.config.intermediate_size % 8 == 0):
+                return self._fused_prefill(idx, input_pos)
             cos = self.cos.index_select(0, input_pos)
             sin = self.sin.index_select(0, input_pos)
             mask = self.mask_cache.index_select(2, input_pos)
@@ -219,6 +222,41 @@ class GPT(nn.Module):
                 comm = False
         self.__dict__["_p2p"] = comm
         return comm or None
+
+    def _fused_prefill(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
+        """T > 1 tokens over the cache with this library's kernels only (reference: model.py:499-519, 572-593, 609-665, 712-716): the
+        embedding, the residual adds fused into the RMSNorm that follows them (b200_rmsnorm delta / sum_out), SwiGLU as one kernel,
+        RoPE + cache append + causal attention straight from the full cos / sin tables and input_pos -- no table or mask
+        `index_select` (the 16 MB mask gather at T = 4096 fed nothing: the attention kernel derives the mask row from input_pos)."""
+        c = self.config
+        B, T = idx.shape
+        eps = c.norm_eps
+        tp = self.tp_world_size > 1
+        scale = 1.0 / math.sqrt(c.head_size)
+        x = K.embedding(idx.reshape(B * T), self.transformer.wte.weight)            # (B*T, d)
+        delta: Optional[torch.Tensor] = None
+        for block in self.transformer.h:
+            a, m, cache = block.attn, block.mlp, block.attn.kv_cache
+            if delta is None:
+                n1 = K.rmsnorm(x, block.norm_1.weight, eps)
+            else:                                                                      # x = x + mlp output, then norm_1
+                x_new = torch.empty_like(x)
+                n1 = K.rmsnorm(x, block.norm_1.weight, eps, delta=delta, sum_out=x_new)
+                x = x_new
+            qkv = a.attn(n1.view(B, T, -1))
+            q = K.rope_kv_append(qkv, self.cos, self.sin, input_pos, cache.k, cache.v, c.n_head, c.n_query_groups, c.head_size,
+                                 c.rope_n_elem, table_preselected=False)
+            y = K.attn_prefill(q, cache.k, cache.v, input_pos, scale)
+            h = a.proj(y)
+            if tp:
+                h = self._all_reduce(h.contiguous())
+            x_new = torch.empty_like(x)
+            n2 = K.rmsnorm(x, block.norm_2.weight, eps, delta=h.view(B * T, -1), sum_out=x_new)   # x = h + x, then norm_2
+            x = x_new
+            n2 = n2.view(B, T, -1)
+            delta = m(n2).view(B * T, -1)   # LLaMAMLP.forward: fused SwiGLU (b200_swiglu, or the GEMV epilogue for <= 16 rows); its tensor-parallel hook sums the ranks' partials
+        xf = K.rmsnorm(x, self.transformer.ln_f.weight, eps, delta=delta)
+        return self.lm_head(xf.view(B, T, -1))
 
     def _fused_decode(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
         """One token per sequence.  Same math as Block.forward / CausalSelfAttention.forward / LLaMAMLP.forward of
@@ -471,7 +509,11 @@ class LLaMAMLP(nn.Module):
             return self.proj(f1.gemv(x, other=f2))
         x_fc_1 = self.fc_1(x)
         x_fc_2 = self.fc_2(x)
-        x = F.silu(x_fc_1) * x_fc_2
+        if (x_fc_1.is_cuda and x_fc_1.dtype == torch.bfloat16 and x_fc_1.numel() % 8 == 0 and not torch.compiler.is_compiling()
+                and isinstance(f1, QLinear)):
+            x = K.swiglu(x_fc_1, x_fc_2)   # one kernel, the reference's rounding points (silu to bf16, product to bf16)
+        else:
+            x = F.silu(x_fc_1) * x_fc_2
         return self.proj(x)
 
 
