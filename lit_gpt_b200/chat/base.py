@@ -46,7 +46,8 @@ def generate(
     token = generate_base.next_token(model, input_pos, prompt.view(1, -1), temperature=temperature, top_k=top_k)
     dg = None
     fused = getattr(model, "fused_decode_ready", None)
-    if prompt.is_cuda and fused is not None and model.fused_decode_ready(prompt.view(1, -1)) and max_returned_tokens - T > 1:
+    if prompt.is_cuda and fused is not None and model.fused_decode_ready(prompt.view(1, -1)) and max_returned_tokens - T > 1 \
+            and not model.spans_devices():
         dg = generate_base._decode_graph_for(model, temperature, top_k, prompt.dtype)
         dg.token.copy_(token.view(-1))
         dg.pos.fill_(T)

@@ -188,11 +188,11 @@ template <int HS, typename PosT>
 cudaError_t launch_prefill(const void* q, const void* kc, const void* vc, const void* pos, void* y, int B, int T, int H, int G, int max_seq,
                            float scale, cudaStream_t st) {
   const size_t smem = (size_t)(kPfBM + 4 * kPfBN) * HS * 2;
-  static std::atomic<int> configured{0};
-  if (!configured.load(std::memory_order_acquire)) {
+  static PerDeviceOnce once;
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(attn_prefill_kernel<HS, PosT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    configured.store(1, std::memory_order_release);
+    once.done();
   }
   dim3 grid((T + kPfBM - 1) / kPfBM, H, B);
   return launch(attn_prefill_kernel<HS, PosT>, grid, dim3(kPfThreads), smem, st, (const __nv_bfloat16*)q, (const __nv_bfloat16*)kc,

@@ -56,6 +56,14 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
 
 int sm_count();
 
+// Kernel attributes (cudaFuncSetAttribute) are per DEVICE: remember on which devices an instantiation has been configured, so that
+// one process driving several GPUs (generate/sequentially.py) configures each of them.
+struct PerDeviceOnce {
+  std::atomic<unsigned long long> mask{0};
+  bool need() const { int d = 0; cudaGetDevice(&d); return ((mask.load(std::memory_order_acquire) >> (d & 63)) & 1ull) == 0; }
+  void done() { int d = 0; cudaGetDevice(&d); mask.fetch_or(1ull << (d & 63), std::memory_order_release); }
+};
+
 // ---- device helpers ---------------------------------------------------------------------------------------
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }

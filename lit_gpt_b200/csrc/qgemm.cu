@@ -272,11 +272,11 @@ static EncodeTiledFn encode_tiled() {
 template <int MT>
 static cudaError_t launch_gemm(const GemmParams& p, cudaStream_t st) {
   constexpr int smem = kGStages * (MT + 1) * kTileBytes + 1024;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce once;
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(qgemm_tcgen05_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    configured = true;
+    once.done();
   }
   // tensor map of x (M, K) bf16 row-major: dim0 = K (contiguous), dim1 = M; box 64 x 128, 128-byte swizzle, zero fill
   EncodeTiledFn enc = encode_tiled();

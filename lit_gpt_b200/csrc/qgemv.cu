@@ -474,11 +474,11 @@ template <int KS, int NB, bool INT4>
 static cudaError_t launch_fast(const GemvParams& p, int gx, int S, cudaStream_t st) {
   constexpr int COLS = 8 * NB;
   const size_t smem = kLutBytes + sizeof(float) * (2 * kGemvWarps * 16 * COLS + kGemvWarps * 16 + 16) + 16;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
+  static PerDeviceOnce once;  // per instantiation
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(qgemv_fast_kernel<KS, NB, INT4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    configured = true;
+    once.done();
   }
   return launch(qgemv_fast_kernel<KS, NB, INT4>, dim3(gx, S), dim3(kGemvThreads), smem, st, p);
 }

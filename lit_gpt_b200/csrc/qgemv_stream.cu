@@ -560,11 +560,11 @@ static std::atomic<int> g_stream_depth{0}, g_stream_occ{0}, g_stream_pf{0};  // 
 
 template <int NB, bool INT4>
 static cudaError_t launch_stream(const StreamParams& p, int gx, cudaStream_t st) {
-  static bool configured = false;  // per instantiation
-  if (!configured) {
+  static PerDeviceOnce once;  // per instantiation
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(qgemv_stream_kernel<NB, INT4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDynSmem);
     if (e != cudaSuccess) return e;
-    configured = true;
+    once.done();
   }
   return launch(qgemv_stream_kernel<NB, INT4>, dim3(gx), dim3(kSThreadsAll), (size_t)kDynSmem, st, p);
 }

@@ -1108,44 +1108,44 @@ void qgemv_v4_tune_kvhint(int on) { g_v4_kvhint = on; }
 
 template <int RU, bool INT4>
 static cudaError_t launch_v4_occ2(const V4Params& p, int gx, cudaStream_t st) {
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceOnce once;
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(qgemv_v4_kernel<RU, INT4, 0, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kV4DynSmem2);
     if (e != cudaSuccess) return e;
-    configured = true;
+    once.done();
   }
   return launch(qgemv_v4_kernel<RU, INT4, 0, false, 2>, dim3(gx), dim3(kV4Threads), (size_t)kV4DynSmem2, st, p);
 }
 
 template <int RU, bool INT4, int MODE, bool XREG>
 static cudaError_t launch_v4(const V4Params& p, int gx, cudaStream_t st) {
-  static bool configured = false;  // per instantiation
-  if (!configured) {
+  static PerDeviceOnce once;  // per instantiation
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(qgemv_v4_kernel<RU, INT4, MODE, XREG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kV4DynSmem);
     if (e != cudaSuccess) return e;
-    configured = true;
+    once.done();
   }
   return launch(qgemv_v4_kernel<RU, INT4, MODE, XREG>, dim3(gx), dim3(kV4Threads), (size_t)kV4DynSmem, st, p);
 }
 
 template <int RU, bool INT4, int MODE>
 static cudaError_t launch_v4_win(const V4Params& p, int gx, cudaStream_t st) {
-  static bool configured = false;  // per instantiation
-  if (!configured) {
+  static PerDeviceOnce once;  // per instantiation
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(qgemv_v4_kernel<RU, INT4, MODE, false, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kV4DynSmem);
     if (e != cudaSuccess) return e;
-    configured = true;
+    once.done();
   }
   return launch(qgemv_v4_kernel<RU, INT4, MODE, false, 1, true>, dim3(gx), dim3(kV4Threads), (size_t)kV4DynSmem, st, p);
 }
 
 template <int RU, bool INT4, bool XREG>
 static cudaError_t launch_v4_att(const V4Params& p, int gx, cudaStream_t st) {
-  static bool configured = false;  // per instantiation
-  if (!configured) {
+  static PerDeviceOnce once;  // per instantiation
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(qgemv_v4_kernel<RU, INT4, 0, XREG, 1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kV4DynSmem);
     if (e != cudaSuccess) return e;
-    configured = true;
+    once.done();
   }
   return launch(qgemv_v4_kernel<RU, INT4, 0, XREG, 1, false, true>, dim3(gx), dim3(kV4Threads), (size_t)kV4DynSmem, st, p);
 }

@@ -138,7 +138,8 @@ def generate(model: GPT, prompt: torch.Tensor, max_returned_tokens: int, *, temp
     tokens.append(token)
     n_steps = max_returned_tokens - T - 1
 
-    if n_steps > 0 and prompt.is_cuda and model.fused_decode_ready(prompt.view(1, -1)):
+    # (a model whose blocks sit on several devices -- generate/sequentially.py -- is driven by one process: no single CUDA graph)
+    if n_steps > 0 and prompt.is_cuda and model.fused_decode_ready(prompt.view(1, -1)) and not model.spans_devices():
         dg = _decode_graph_for(model, temperature, top_k, prompt.dtype)
         dg.token.copy_(token)
         dg.pos.fill_(T)

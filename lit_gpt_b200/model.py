@@ -144,6 +144,8 @@ class GPT(nn.Module):
 
     def _apply(self, fn, recurse: bool = True):
         self._fused_plan = None  # device moves quantize the Linears: re-plan on the next forward
+        self.__dict__.pop("_spans", None)
+        self.__dict__.pop("_seq_tables", None)
         self.__dict__.pop("_p2p", None)
         self.__dict__.pop("_decode_graphs", None)  # captured graphs pin the kv / table / weight buffers
         return super()._apply(fn, recurse)
@@ -223,6 +225,23 @@ class GPT(nn.Module):
         self.__dict__["_p2p"] = comm
         return comm or None
 
+    # ---- blocks placed on several devices by generate/sequentially.py ----------------------------------------------------
+    def spans_devices(self) -> bool:
+        hit = self.__dict__.get("_spans")
+        if hit is None:
+            hit = self.__dict__["_spans"] = len({b.norm_1.weight.device for b in self.transformer.h}) > 1
+        return hit
+
+    def _tables_on(self, dev: torch.device) -> Tuple[torch.Tensor, torch.Tensor]:
+        """cos / sin on `dev` (every device of a sequentially placed model keeps its own copy of the RoPE tables)."""
+        if dev == self.cos.device:
+            return self.cos, self.sin
+        tabs = self.__dict__.setdefault("_seq_tables", {})
+        hit = tabs.get(dev)
+        if hit is None or hit[2] != self.cos.data_ptr():
+            hit = tabs[dev] = (self.cos.to(dev), self.sin.to(dev), self.cos.data_ptr())
+        return hit[0], hit[1]
+
     def _fused_prefill(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
         """T > 1 tokens over the cache with this library's kernels only (reference: model.py:499-519, 572-593, 609-665, 712-716): the
         embedding, the residual adds fused into the RMSNorm that follows them (b200_rmsnorm delta / sum_out), SwiGLU as one kernel,
@@ -233,6 +252,8 @@ class GPT(nn.Module):
         eps = c.norm_eps
         tp = self.tp_world_size > 1
         scale = 1.0 / math.sqrt(c.head_size)
+        if self.spans_devices():
+            return self._fused_prefill_multi(idx, input_pos)
         x = K.embedding(idx.reshape(B * T), self.transformer.wte.weight)            # (B*T, d)
         delta: Optional[torch.Tensor] = None
         for block in self.transformer.h:
@@ -258,12 +279,81 @@ class GPT(nn.Module):
         xf = K.rmsnorm(x, self.transformer.ln_f.weight, eps, delta=delta)
         return self.lm_head(xf.view(B, T, -1))
 
+    def _fused_prefill_multi(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
+        """_fused_prefill for blocks placed on several devices (generate/sequentially.py): the residual stream and the pending
+        branch output hop to the next device when a block lives elsewhere; every launch runs with its device current."""
+        c = self.config
+        B, T = idx.shape
+        eps, scale = c.norm_eps, 1.0 / math.sqrt(c.head_size)
+        root = self.transformer.wte.weight.device
+        with torch.cuda.device(root):
+            x = K.embedding(idx.reshape(B * T), self.transformer.wte.weight)
+        delta: Optional[torch.Tensor] = None
+        for block in self.transformer.h:
+            dev = block.norm_1.weight.device
+            a, m, cache = block.attn, block.mlp, block.attn.kv_cache
+            with torch.cuda.device(dev):
+                if x.device != dev:
+                    x = x.to(dev, non_blocking=True)
+                    delta = None if delta is None else delta.to(dev, non_blocking=True)
+                cos, sin = self._tables_on(dev)
+                pos = input_pos if input_pos.device == dev else input_pos.to(dev, non_blocking=True)
+                if delta is None:
+                    n1 = K.rmsnorm(x, block.norm_1.weight, eps)
+                else:
+                    x_new = torch.empty_like(x)
+                    n1 = K.rmsnorm(x, block.norm_1.weight, eps, delta=delta, sum_out=x_new)
+                    x = x_new
+                qkv = a.attn(n1.view(B, T, -1))
+                q = K.rope_kv_append(qkv, cos, sin, pos, cache.k, cache.v, c.n_head, c.n_query_groups, c.head_size, c.rope_n_elem,
+                                     table_preselected=False)
+                h = a.proj(K.attn_prefill(q, cache.k, cache.v, pos, scale))
+                x_new = torch.empty_like(x)
+                n2 = K.rmsnorm(x, block.norm_2.weight, eps, delta=h.view(B * T, -1), sum_out=x_new)
+                x = x_new
+                delta = m.proj(K.swiglu(m.fc_1(n2.view(B, T, -1)), m.fc_2(n2.view(B, T, -1)))).view(B * T, -1)
+        with torch.cuda.device(root):
+            if x.device != root:
+                x, delta = x.to(root, non_blocking=True), delta.to(root, non_blocking=True)
+            xf = K.rmsnorm(x, self.transformer.ln_f.weight, eps, delta=delta)
+            return self.lm_head(xf.view(B, T, -1))
+
+    def _fused_decode_multi(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
+        """_fused_decode for blocks placed on several devices: the same five launches per block, each device segment on its own
+        GPU; the 8 KB residual stream crosses NVLink once per device boundary."""
+        c = self.config
+        B = idx.size(0)
+        eps = c.norm_eps
+        root = self.transformer.wte.weight.device
+        with torch.cuda.device(root):
+            x = K.embedding(idx.view(B), self.transformer.wte.weight)
+        for block in self.transformer.h:
+            dev = block.norm_1.weight.device
+            a, m, cache = block.attn, block.mlp, block.attn.kv_cache
+            with torch.cuda.device(dev):
+                if x.device != dev:
+                    x = x.to(dev, non_blocking=True)
+                cos, sin = self._tables_on(dev)
+                pos = input_pos if input_pos.device == dev else input_pos.to(dev, non_blocking=True)
+                qkv = a.attn.gemv(x, norm_weight=block.norm_1.weight, norm_eps=eps, kv_hint=(cache.k, cache.v, pos))
+                y = K.attn_decode(qkv, cos, sin, pos, cache.k, cache.v, c.n_head, c.n_query_groups, c.head_size, c.rope_n_elem)
+                x = a.proj.gemv(y, residual=x)
+                act = m.fc_1.gemv(x, other=m.fc_2, norm_weight=block.norm_2.weight, norm_eps=eps)
+                x = m.proj.gemv(act, residual=x)
+        with torch.cuda.device(root):
+            if x.device != root:
+                x = x.to(root, non_blocking=True)
+            logits = self.lm_head.gemv(x, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+        return logits.view(B, 1, -1)
+
     def _fused_decode(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
         """One token per sequence.  Same math as Block.forward / CausalSelfAttention.forward / LLaMAMLP.forward of
         the reference (model.py:572-593, 609-656, 712-716) with identical bf16 rounding points."""
         c = self.config
         B = idx.size(0)
         tp = self.tp_world_size > 1
+        if not tp and self.spans_devices():
+            return self._fused_decode_multi(idx, input_pos)
         x = K.embedding(idx.view(B), self.transformer.wte.weight)  # (B, d_full)
         delta: Optional[torch.Tensor] = None
         eps = c.norm_eps

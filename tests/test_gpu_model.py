@@ -318,6 +318,66 @@ def test_tp2_matches_oracle_multi_gpu(mode, inter):
     print(out.stdout[-500:])
 
 
+def _sequential_model(kw, p, mode, devices, max_seq):
+    """The load flow of generate/sequentially.py:171-190: weights on the CPU, QLinear modules swapped in, then placed."""
+    from lit_gpt_b200 import GPT, Config, QuantPrecision
+    from lit_gpt_b200.generate.sequentially import sequential
+
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(torch.bfloat16)
+    try:
+        with torch.device("meta"):
+            model = GPT(Config(**kw))
+    finally:
+        torch.set_default_dtype(prev)
+    model.load_state_dict({k: v.to(torch.bfloat16) for k, v in p.items()}, assign=True)
+    model = QuantPrecision(mode, torch.bfloat16).convert_module(model).eval()
+    return sequential(model, torch.device("cuda", 0), max_seq, devices)
+
+
+@pytest.mark.parametrize("devices", [1, 2])
+@torch.inference_mode()
+def test_sequential_placement_matches_single_device(golden, devices):
+    """generate/sequentially.py:31-97: blocks placed over `devices` GPUs by one process give the logits and the
+    greedy tokens of the same quantized model on one GPU, bit for bit (same kernels, the residual stream hops devices)."""
+    if torch.cuda.device_count() < devices:
+        pytest.skip(f"needs {devices} GPUs")
+    import lit_gpt_b200.generate.base as gb
+    from lit_gpt_b200.generate.sequentially import move_block_input, move_block_output
+
+    g = golden("llama_gqa_hs64")
+    cfgd, kw = cfg_from_golden(g)
+    p = M.init_weights(M.RefConfig.from_any(cfgd), seed=1234)
+    single = build_cuda_model(kw, p, "nf4", max_seq=40)
+    prompt = torch.from_numpy(g["gen_prompt"]).cuda()
+    T = prompt.numel()
+    y1 = single(prompt.view(1, -1), torch.arange(T, device="cuda")).float().cpu()
+    d1 = single(torch.tensor([[7]], device="cuda"), torch.tensor([T], device="cuda")).float().cpu()
+    for blk in single.transformer.h:
+        blk.attn.kv_cache.reset_parameters()
+    t1 = gb.generate(single, prompt, 30, temperature=0.0).cpu()
+    model = _sequential_model(kw, p, "nf4", devices, 40)
+    n_layer = cfgd["n_layer"]
+    devs = [str(b.attn.attn.weight.device) for b in model.transformer.h]
+    assert devs == [f"cuda:{i // (n_layer // devices)}" for i in range(n_layer)]
+    assert all(str(b.attn.kv_cache.k.device) == d for b, d in zip(model.transformer.h, devs))
+    assert str(model.lm_head.weight.device) == "cuda:0" and model.max_seq_length == 40
+    if devices > 1:   # the reference's hook placement (tests/test_generate_sequentially.py:157-260)
+        last = model.transformer.h[-1]
+        assert [h.func for h in last._forward_hooks.values()] == [move_block_output]
+        assert all(([h.func for h in b._forward_pre_hooks.values()] == [move_block_input]) == (i >= n_layer // devices)
+                   for i, b in enumerate(model.transformer.h))
+        assert model.spans_devices()
+    assert model.fused_decode_ready()
+    y2 = model(prompt.view(1, -1), torch.arange(T, device="cuda")).float().cpu()
+    d2 = model(torch.tensor([[7]], device="cuda"), torch.tensor([T], device="cuda")).float().cpu()
+    assert torch.equal(y1, y2) and torch.equal(d1, d2)
+    for blk in model.transformer.h:
+        blk.attn.kv_cache.reset_parameters()
+    t2 = gb.generate(model, prompt, 30, temperature=0.0).cpu()
+    assert torch.equal(t1, t2)
+
+
 @torch.inference_mode(False)
 def test_traced_forward_has_no_graph_breaks():
     """Mirror of the reference's tests/test_model.py:564-575: dynamo traces GPT.forward (prefill and the cached decode call)
