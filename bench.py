@@ -114,7 +114,7 @@ def build_random_model(cfg_name: str, mode: str, max_seq: int, batch: int, fabri
     """Random-init weights of the named architecture (N(0, 0.02), seed 1234, bf16), materialised one matrix at a
     time on the GPU, sharded in full precision (generate/tp.py order) and then quantized by the library."""
     from lit_gpt_b200 import GPT, Config, QLinear
-    from lit_gpt_b200.generate.tp import tensor_parallel
+    from lit_gpt_b200.generate.tp import shard_lm_head, tensor_parallel
 
     kw = {} if n_layer is None else {"n_layer": n_layer}
     cfg = Config.from_name(cfg_name, **kw)
@@ -125,8 +125,12 @@ def build_random_model(cfg_name: str, mode: str, max_seq: int, batch: int, fabri
     styles = {}
     if fabric.world_size > 1:
         model = tensor_parallel(fabric, model)
+        if os.environ.get("B200_TP_SHARD_LM_HEAD", "1") == "1":   # §8f-3: vocabulary slices per rank, all-gathered over peer memory
+            model = shard_lm_head(fabric, model)
         for n in full_shapes:
             styles[n] = 0 if n.endswith(("attn.attn", "fc_1", "fc_2", "fc")) else (1 if n.endswith("proj") else None)
+        if getattr(model, "lm_head_sharded", False):
+            styles["lm_head"] = 0
     dev = fabric.device
     gen = torch.Generator(device=dev)
     for i, (name, mod) in enumerate(model.named_modules()):
@@ -151,13 +155,13 @@ def build_random_model(cfg_name: str, mode: str, max_seq: int, batch: int, fabri
     return model, full
 
 
-def step_bytes(full_cfg, mode: str, ctx: int, batch: int, tp: int) -> dict:
+def step_bytes(full_cfg, mode: str, ctx: int, batch: int, tp: int, head_sharded: bool = False) -> dict:
     """Algorithmic HBM bytes of one decode step per GPU: packed weights + scales of every Linear once,
     plus the filled KV rows at n_query_groups heads in bf16.  lm_head is replicated under TP (generate/tp.py:77-80)."""
     c = full_cfg
     per_layer = c.n_embd * (c.n_head + 2 * c.n_query_groups) * c.head_size + c.n_embd * c.n_embd + 3 * c.n_embd * c.intermediate_size
     head = c.padded_vocab_size * c.n_embd
-    w = (c.n_layer * per_layer / tp + head) * BPP[mode]
+    w = (c.n_layer * per_layer / tp + head / (tp if head_sharded else 1)) * BPP[mode]
     kv = 2 * c.n_layer * c.n_query_groups * c.head_size * 2 * ctx * batch / tp
     return {"weights": w, "kv": kv, "total": w + kv}
 
@@ -359,7 +363,7 @@ def run_ours(args) -> None:
     clocks = sampler.stop() if rank == 0 else {}
     tok_s = batch * K_steps / (ms / 1e3)
     ctx_mid = ctx + T + W + K_steps // 2
-    bytes_step = step_bytes(full_cfg, mode, ctx_mid, batch, world)
+    bytes_step = step_bytes(full_cfg, mode, ctx_mid, batch, world, bool(getattr(model, "lm_head_sharded", False)))
 
     # ---- dominant kernel in isolation: the dequant-GEMV launches of one step, same weights (3.7 GB >> L2) ----
     x = torch.randn(batch, model.transformer.wte.weight.shape[1], device=dev).to(torch.bfloat16)
@@ -433,7 +437,7 @@ def run_ours(args) -> None:
         "value": tok_s, "unit": "tokens/s", "n_gpus": world, "steps": K_steps, "warmup": W, "ms_per_step": ms / K_steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": args.workload, "model": cfg_name, "quantize": mode, "batch": batch, "prompt_tokens": T,
-                   "context_prefill": ctx, "max_seq": max_seq, "parallelism": f"tp{world}", "n_layer": full_cfg.n_layer,
+                   "context_prefill": ctx, "max_seq": max_seq, "parallelism": f"tp{world}", "lm_head_sharded": bool(getattr(model, "lm_head_sharded", False)), "n_layer": full_cfg.n_layer,
                    "l2_policy": "weights per step (>= 0.4 GB/GPU) exceed the 126 MB L2; no flush needed",
                    "bytes_per_step": bytes_step, "build_s": round(t_build, 1)},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * K_steps), "launches_per_step": int(launches_per_step),

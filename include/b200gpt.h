@@ -143,6 +143,13 @@ typedef struct b200_tp_handoff {
   void* recv_seq;         /* consumer: LOCAL sequence counter of the buffer read (bumped by the launch's last CTA) */
   void* recv_done;        /* consumer: local CTA counter */
 } b200_tp_handoff;
+/* All-gather over the same slots (`lm_head` sharded by rows under tensor parallelism; the reference replicates it,
+ * generate/tp.py:77-80).  The sharded Linear's GEMV is launched as a PRODUCER (tp->send_seq / peer_y set, y may be NULL): rank r's
+ * (batch, N / world) outputs land in slot r of every rank's gather buffer.  This call is the CONSUMER: it polls the `world` slots of
+ * the local buffer (consumer fields of `h`), unpacks them into out (batch, world * n_per_rank) bf16 in rank order -- i.e. the
+ * unsharded Linear's output -- and bumps the buffer's sequence counter.  The gather buffer is a third hand-off buffer with its own
+ * counters (it must not be one of the two alternating branch buffers).  error_word: optional, set to 2 on a bounded-wait time-out. */
+int b200_tp_gather(const b200_tp_handoff* h, int batch, int64_t n_per_rank, void* out, void* error_word, b200_stream_t stream);
 /* Symmetric peer buffers (setup time, not per token): cudaMalloc + zero + IPC export / import / release. */
 int b200_p2p_alloc(size_t bytes, void** ptr, void* handle64);
 int b200_p2p_open(const void* handle64, void** ptr);

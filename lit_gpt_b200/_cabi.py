@@ -115,6 +115,7 @@ _SIGNATURES = {
                                     c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_attn_prefill": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                   c_float, c_void_p]),
+    "b200_tp_gather": (c_int, [ctypes.POINTER(TpHandoff), c_int, c_int64, c_void_p, c_void_p, c_void_p]),
     "b200_swiglu": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "b200_embedding": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p]),
     "b200_argmax": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int, c_void_p, c_int, c_void_p, c_int64, c_void_p]),

@@ -71,6 +71,33 @@ def all_reduce_output(world_size: int, module: torch.nn.Module, ins: Any, outs: 
     return outs
 
 
+def all_gather_output(world_size: int, module: torch.nn.Module, ins: Any, outs: torch.Tensor) -> torch.Tensor:
+    """Module-path hook of a row-sharded lm_head (prefill, non-fused models): concatenate the ranks' vocabulary slices."""
+    if world_size > 1 and dist.is_available() and dist.is_initialized():
+        outs = outs.contiguous()
+        parts = [torch.empty_like(outs) for _ in range(world_size)]
+        dist.all_gather(parts, outs)
+        outs = torch.cat(parts, dim=-1)
+    return outs
+
+
+def shard_lm_head(fabric: Any, model: GPT) -> GPT:
+    """NOT in the reference (generate/tp.py:77-80 leaves `lm_head` replicated; SURVEY §8f-3 lists this as the next step): shard
+    `lm_head` by rows (vocabulary slices) so that each rank streams 1 / world of it.  Call after `tensor_parallel`, before the
+    move to the GPU.  Decode: the slices are all-gathered over the peer-memory slots (b200_tp_gather) and every rank holds the full
+    logits, bit-identical to the replicated Linear; prefill / module path: `all_gather` hook.  Skipped (model unchanged) when the
+    vocabulary does not split into 16-row tiles."""
+    world_size = fabric.world_size
+    head = model.lm_head
+    if world_size < 2 or head.out_features % world_size or (head.out_features // world_size) % 16 or head.bias is not None:
+        return model
+    tensor_parallel_linear(fabric, head, "colwise")
+    head.register_forward_hook(partial(all_gather_output, world_size))
+    model.lm_head_sharded = True
+    model._fused_plan = None
+    return model
+
+
 def tensor_parallel(fabric: Any, model: GPT) -> GPT:
     for block in model.transformer.h:
         tensor_parallel_mlp(fabric, block.mlp)
@@ -148,6 +175,10 @@ def main(
 
             t0 = time.perf_counter()
             model = tensor_parallel(fabric, model)
+            import os
+
+            if fabric._precision is not None and os.environ.get("B200_TP_SHARD_LM_HEAD", "1") == "1":
+                model = shard_lm_head(fabric, model)  # beyond the reference (tp.py:77-80 replicates it): vocabulary slices per rank
             print(f"[{rank}] Time to tensor-parallelize the model: {time.perf_counter() - t0:.02f} seconds.", file=sys.stderr)
 
             with fabric.init_tensor():

@@ -342,6 +342,14 @@ def qgemv_tiled_supported(N: int, K: int, quant_type: str, batch: int, swiglu: b
     return _qgemv_tiled_supported(int(N), int(K), quant_type, int(batch), bool(swiglu), int(fold))
 
 
+def tp_gather(h: "C.TpHandoff", batch: int, n_per_rank: int, device: torch.device) -> torch.Tensor:
+    """All-gather of a row-sharded Linear's outputs over the peer-memory slots -> (batch, world * n_per_rank) bf16."""
+    out = torch.empty((batch, h.world * n_per_rank), dtype=torch.bfloat16, device=device)
+    ws = _ws("qgemv_tiled", device, C.load().b200_qgemv_tiled_workspace_bytes())
+    C.check(C.load().b200_tp_gather(ctypes.byref(h), batch, n_per_rank, out.data_ptr(), ws.data_ptr(), C.stream_ptr(device)), "tp_gather")
+    return out
+
+
 def check_gemv_errors(device: torch.device) -> None:
     """Raise if a GEMV kernel on `device` gave up a bounded wait (a tensor-parallel peer that never delivered its
     packets, a stream-K partner CTA): synchronizes the current stream.  Called by generate() at its sync points."""

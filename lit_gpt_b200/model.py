@@ -216,7 +216,8 @@ class GPT(nn.Module):
         if ok:
             try:
                 d_full = blocks[0].attn.proj.out_features
-                comm = PeerComm(self.tp_group, self.transformer.wte.weight.device, 16 * d_full * 4)  # 32-bit packets
+                gather = 16 * self.lm_head.out_features * 4 if getattr(self, "lm_head_sharded", False) else 0
+                comm = PeerComm(self.tp_group, self.transformer.wte.weight.device, 16 * d_full * 4, gather)  # 32-bit packets
             except Exception as e:  # consistent on all ranks (PeerComm agrees on failure collectively)
                 import warnings
 
@@ -346,6 +347,13 @@ class GPT(nn.Module):
             logits = self.lm_head.gemv(x, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
         return logits.view(B, 1, -1)
 
+    def _gather_dummy(self, B: int, n: int, device: torch.device) -> torch.Tensor:
+        """The sharded lm_head's local slice is also stored locally (y): a persistent scratch row, not a per-step allocation."""
+        t = self.__dict__.get("_gather_y")
+        if t is None or t.shape != (B, n) or t.device != device:
+            t = self.__dict__["_gather_y"] = torch.empty((B, n), dtype=torch.bfloat16, device=device)
+        return t
+
     def _fused_decode(self, idx: torch.Tensor, input_pos: torch.Tensor) -> torch.Tensor:
         """One token per sequence.  Same math as Block.forward / CausalSelfAttention.forward / LLaMAMLP.forward of
         the reference (model.py:572-593, 609-656, 712-716) with identical bf16 rounding points."""
@@ -398,10 +406,24 @@ class GPT(nn.Module):
                     pending = "p2p"
                 else:
                     pending = self._all_reduce(lin(m.proj, act))
-            if isinstance(pending, str):
-                logits = tlin(self.lm_head, x, recv=1, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+            head = self.lm_head
+            if getattr(self, "lm_head_sharded", False):
+                # lm_head sharded by rows (§8f-3): this rank's vocabulary slice goes straight from the GEMV's epilogue into every
+                # rank's gather buffer; b200_tp_gather unpacks the full logits (a third buffer: the two branch buffers alternate)
+                hs = comm.gather_send()
+                if isinstance(pending, str):
+                    hr = comm.handoff(None, 1)
+                    hs.slots, hs.slot_stride, hs.recv_seq, hs.recv_done, hs.reduced = hr.slots, hr.slot_stride, hr.recv_seq, hr.recv_done, hr.reduced
+                    K.qgemv_tiled(x, head.tiled, head.out_features, head.in_features, head.quant_type, head.blocksize, tp=hs,
+                                  norm_weight=self.transformer.ln_f.weight, norm_eps=eps, out=self._gather_dummy(B, head.out_features, x.device))
+                else:
+                    K.qgemv_tiled(x, head.tiled, head.out_features, head.in_features, head.quant_type, head.blocksize, tp=hs, delta=pending,
+                                  norm_weight=self.transformer.ln_f.weight, norm_eps=eps, out=self._gather_dummy(B, head.out_features, x.device))
+                logits = K.tp_gather(comm.gather_recv(), B, head.out_features, x.device)
+            elif isinstance(pending, str):
+                logits = tlin(head, x, recv=1, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
             else:
-                logits = lin(self.lm_head, x, delta=pending, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+                logits = lin(head, x, delta=pending, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
             return logits.view(B, 1, -1)
         import os
 
@@ -446,6 +468,12 @@ class GPT(nn.Module):
                 x = lin(m.proj, act, nxt_qkv, residual=x)
         first = blocks[0].attn.attn if blocks else None  # graph replays run back to back: wrap the prefetch around
         logits = lin(self.lm_head, x, first, delta=delta, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+        if tp and getattr(self, "lm_head_sharded", False):   # all-NCCL tensor-parallel path (B200_TP_NCCL=1): gather the vocabulary slices
+            import torch.distributed as dist
+
+            parts = [torch.empty_like(logits) for _ in range(self.tp_world_size)]
+            dist.all_gather(parts, logits.contiguous(), group=self.tp_group)
+            logits = torch.cat(parts, dim=-1)
         return logits.view(B, 1, -1)
 
 

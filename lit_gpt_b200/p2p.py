@@ -26,7 +26,7 @@ FLAG_BLOCK = 128
 
 
 class PeerComm:
-    def __init__(self, group, device: torch.device, slot_bytes: int) -> None:
+    def __init__(self, group, device: torch.device, slot_bytes: int, gather_slot_bytes: int = 0) -> None:
         import torch.distributed as dist
 
         self.group = group
@@ -44,7 +44,10 @@ class PeerComm:
         import os
 
         self.two_stage = self.world >= int(os.environ.get("B200_TP_TWO_STAGE_MIN", "99"))
-        total = self.data_bytes + 2 * FLAG_BLOCK + 2 * self.slot_bytes
+        # third buffer with its own counters: all-gather of a row-sharded lm_head (b200_tp_gather); 0 = none
+        self.gather_slot_bytes = (int(gather_slot_bytes) + 255) & ~255
+        self.gather_off = self.data_bytes + 2 * FLAG_BLOCK + 2 * self.slot_bytes
+        total = self.gather_off + self.world * self.gather_slot_bytes + FLAG_BLOCK
         lib = C.load()
         self._local, self._opened, self.base = 0, [], []
         # every stage is followed by a collective agreement, so that a failure on one rank fails all of them the same way
@@ -105,6 +108,25 @@ class PeerComm:
             h.recv_done = self._flags(self._local, recv) + 32
             if self.two_stage:
                 h.reduced = self._local + self.data_bytes + 2 * FLAG_BLOCK + recv * self.slot_bytes
+        return h
+
+    def gather_send(self) -> "C.TpHandoff":
+        """Producer descriptor of the all-gather: this rank's outputs go to slot `rank` of every rank's gather buffer."""
+        h = C.TpHandoff()
+        h.world, h.rank = self.world, self.rank
+        for r in range(self.world):
+            h.peer_y[r] = self.base[r] + self.gather_off + self.rank * self.gather_slot_bytes
+        h.send_seq = self._local + self.gather_off + self.world * self.gather_slot_bytes
+        return h
+
+    def gather_recv(self) -> "C.TpHandoff":
+        """Consumer descriptor of the all-gather (b200_tp_gather)."""
+        h = C.TpHandoff()
+        h.world, h.rank = self.world, self.rank
+        h.slots = self._local + self.gather_off
+        h.slot_stride = self.gather_slot_bytes
+        h.recv_seq = self._local + self.gather_off + self.world * self.gather_slot_bytes
+        h.recv_done = h.recv_seq + 32
         return h
 
     def close(self) -> None:

@@ -22,7 +22,7 @@ sys.path.insert(0, ROOT)
 
 from lit_gpt_b200 import GPT, Config, QuantPrecision  # noqa: E402
 from lit_gpt_b200.fabric import Fabric  # noqa: E402
-from lit_gpt_b200.generate.tp import tensor_parallel  # noqa: E402
+from lit_gpt_b200.generate.tp import shard_lm_head, tensor_parallel  # noqa: E402
 import lit_gpt_b200.generate.base as gb  # noqa: E402
 from oracle import model_ref as M  # noqa: E402
 from oracle import quant_ref as Q  # noqa: E402
@@ -92,6 +92,10 @@ def main() -> None:
     model.load_state_dict(p)
     model = fabric._precision.convert_module(model)
     model = tensor_parallel(fabric, model)
+    head_sharded = os.environ.get("B200_TP_SHARD_LM_HEAD", "0") == "1"
+    if head_sharded:   # lm_head sharded by rows; the oracle is unchanged (whole rows per shard: same code words)
+        model = shard_lm_head(fabric, model)
+        assert model.lm_head.out_features == cfg.padded_vocab_size // world
     with fabric.init_tensor():
         model.max_seq_length = 48
         model.cos, model.sin = model.rope_cache()
@@ -175,7 +179,7 @@ def main() -> None:
             assert e_n <= 2 ** -6 * scale, (e_n, scale)
         seq_now = int(raw_u32(comm._flags(comm._local, 0), 1, dev).item())
     if rank == 0:
-        print(f"[tp{world}/{'shared-gpu' if shared else 'multi-gpu'}/{mode}/H{n_head}G{n_groups}/I{cfg.intermediate_size}] bf16-reference err {e_ref:.4f} cuda err {e_k:.4f} tol {tol:.4f} "
+        print(f"[tp{world}/{'shared-gpu' if shared else 'multi-gpu'}/{mode}/H{n_head}G{n_groups}/I{cfg.intermediate_size}{'/lm_head-sharded' if head_sharded else ''}] bf16-reference err {e_ref:.4f} cuda err {e_k:.4f} tol {tol:.4f} "
               f"(|logit| max {scale:.2f}); top-1 {int(agree.sum())}/{len(agree)} (decisive {int(decisive.sum())}); "
               f"greedy prefix {(div or n_total) - T}/{n_total - T}; hand-off seq {seq0} -> {seq_now}"
               + ("" if e_n is None else f"; |p2p - nccl| {e_n:.4f}"), flush=True)
