@@ -105,8 +105,14 @@ class Fabric:
         return obj
 
 
+SEED_EPOCH = 0  # bumped by every seed_everything call: device-side sampler states reseed when it changes
+
+
 def seed_everything(seed: int) -> int:
     import random
+
+    global SEED_EPOCH
+    SEED_EPOCH += 1
 
     import numpy as np
 

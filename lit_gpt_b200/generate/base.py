@@ -32,14 +32,26 @@ def multinomial_num_samples_1(probs: torch.Tensor) -> torch.Tensor:
     return torch.multinomial(probs, num_samples=1)
 
 
-_RNG: Dict[torch.device, torch.Tensor] = {}
+_RNG: Dict[torch.device, Tuple[torch.Tensor, int, int]] = {}
 
 
 def _rng_for(device: torch.device) -> torch.Tensor:
-    """Per-device Philox state of the fused sampler, (re)seeded from torch's seed so ``seed_everything`` is honoured."""
-    st = _RNG.get(device)
-    if st is None or int(st[0].item()) != (torch.initial_seed() & 0x7FFFFFFFFFFFFFFF):
-        st = _RNG[device] = K.new_rng_state(device)
+    """ONE Philox state per device, shared by the prefill draw and every captured decode graph (separate states with the same seed
+    would replay the same noise: correlated samples).  Reseeded IN PLACE -- captured graphs hold its address -- whenever torch's
+    seed changes or ``seed_everything`` is called again, so that a re-seeded run reproduces like the reference's."""
+    import lit_gpt_b200.fabric as _fabric
+
+    device = torch.device(device.type, device.index if device.index is not None else torch.cuda.current_device())
+    seed, epoch = torch.initial_seed() & 0x7FFFFFFFFFFFFFFF, _fabric.SEED_EPOCH
+    hit = _RNG.get(device)
+    if hit is None:
+        st = K.new_rng_state(device)
+    elif hit[1] != seed or hit[2] != epoch:
+        st = hit[0]
+        st.copy_(torch.tensor([seed, 0], dtype=torch.int64))
+    else:
+        return hit[0]
+    _RNG[device] = (st, seed, epoch)
     return st
 
 
@@ -76,7 +88,7 @@ class DecodeGraph:
         self.pos = torch.zeros(1, dtype=torch.int64, device=dev)
         self.history = torch.zeros(model.max_seq_length + 1, dtype=dtype, device=dev)
         self.max_seq_length = model.max_seq_length
-        self.rng = K.new_rng_state(dev)
+        self.rng = _rng_for(dev)   # the device's one sampler state (shared with the prefill draw)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
 
     def _step(self) -> None:
@@ -130,6 +142,8 @@ def generate(model: GPT, prompt: torch.Tensor, max_returned_tokens: int, *, temp
         raise NotImplementedError(f"max_seq_length {model.max_seq_length} needs to be >= {max_returned_tokens - 1}")
 
     device = prompt.device
+    if device.type == "cuda" and temperature > 0.0:
+        _rng_for(device)   # apply a pending reseed before any draw of this call
     tokens = [prompt]
     input_pos = torch.tensor([T], device=device)
     token = next_token(

@@ -55,9 +55,10 @@ class Tokenizer:
             return False
         with open(path) as fp:
             cfg = json.load(fp)
-        if any(cfg.get(k) is not None for k in ("add_bos_token", "add_prefix_space")):
-            return bool(cfg.get("add_bos_token", cfg.get("tokenizer_class") == "LlamaTokenizer"))
-        return cfg.get("tokenizer_class") == "LlamaTokenizer"
+        # reference lit_gpt/tokenizer.py:78-87: either flag truthy -> BOS; else only a LlamaTokenizer WITHOUT an add_bos_token key
+        if any(cfg.get(k, False) for k in ("add_bos_token", "add_prefix_space")):
+            return True
+        return cfg.get("add_bos_token") is None and cfg.get("tokenizer_class") == "LlamaTokenizer"
 
     def encode(self, string: str, device: Optional[torch.device] = None, bos: Optional[bool] = None, eos: bool = False,
                max_length: int = -1) -> torch.Tensor:

@@ -288,9 +288,16 @@ def test_sampling_path_in_graph(golden):
     p = M.init_weights(M.RefConfig.from_any(cfgd), seed=1234)
     model = build_cuda_model(kw, p, "nf4", max_seq=40)
     prompt = torch.from_numpy(g["gen_prompt"]).cuda()
-    torch.manual_seed(0)
+    from lit_gpt_b200.fabric import seed_everything
+
+    seed_everything(1234)
     out = gb.generate(model, prompt, 30, temperature=0.8, top_k=20)
     assert out.shape[0] == 30 and int(out.max()) < cfgd["padded_vocab_size"]
+    # a second sample continues the device's ONE Philox stream (prefill draw and captured graph share it), a re-seed replays it
+    out_b = gb.generate(model, prompt, 30, temperature=0.8, top_k=20)
+    seed_everything(1234)
+    out_c = gb.generate(model, prompt, 30, temperature=0.8, top_k=20)
+    assert torch.equal(out, out_c) and not torch.equal(out, out_b)
     # eos stops generation (polled) and the eos token itself is kept, as in the reference loop
     greedy = gb.generate(model, prompt, 30, temperature=0.0)
     eos = int(greedy[12])
