@@ -75,6 +75,7 @@ struct V4Params {
   int kvh_i64, kvh_chunks, kvh_row, kvh_max; long long kvh_stride;
   // fused decode attention (b200_qgemv_tiled_args::attn): parameters, 128-thread sub-blocks per head, row tiles per head, counters
   AttnParams att; int att_nsplit, att_tph; unsigned int* att_cnt;
+  int nbuf;         // batch > 1: reduction buffers (2, or 1 when that lets the activation rows fit without k-windows)
   int wu, nwin;     // k-windows (batch > 1 whose activation rows do not fit shared memory): units per tile and window, window count
   int fold;         // row folding (b200_qgemv_tiled_args::fold): N, K, batch above are the FOLDED view; outputs are unfolded
   int64_t Nout;     // true output features (fold * N)
@@ -154,7 +155,10 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
   constexpr int UB = RU * REC;                 // unit bytes
   constexpr int STAGE = kV4CW * UB;
   constexpr int REDW = MODE == 0 ? 16 : 16 * COLS;   // floats per (buffer, warp)
-  constexpr int NBUF = MODE == 0 ? 4 : 2;
+  const int NBUF = MODE == 0 ? 4 : p.nbuf;
+  // nf4 / fp4 at batch > 1: the reduction buffers live in the unused upper halves of the 256-byte table rows (batch 1 keeps its
+  // activation row there), which frees 16 - 32 KB for the activation rows and the ring
+  constexpr bool GAPRED = !INT4 && MODE != 0;
   constexpr int NV = MODE == 0 ? 1 : (16 * COLS) / 32;  // outputs per reducer lane and tile
 
   const uint32_t b0 = smem_u32(smem_raw);
@@ -162,7 +166,7 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
   const int B = p.batch;
   // WIN: p.nkb / p.xstride describe ONE k-window; the per-tile accumulators of the reducer follow the activation rows
   const int tacc_bytes = WIN ? ((((int)((p.U / (p.ts * p.upt)) + (int)gridDim.x - 1) / (int)gridDim.x) * p.ts) * 16 * COLS * 4) : 0;
-  const V4Plan pl = v4_plan(b0, STAGE, NBUF * kV4CW * REDW * 4, INT4, B, p.nkb, p.xstride, p.gap, OCC == 2 ? kV4DynSmem2 : kV4DynSmem, tacc_bytes);
+  const V4Plan pl = v4_plan(b0, STAGE, GAPRED ? 0 : NBUF * kV4CW * REDW * 4, INT4, B, p.nkb, p.xstride, p.gap, OCC == 2 ? kV4DynSmem2 : kV4DynSmem, tacc_bytes);
   const int S = pl.S;
   if (S < 2) __trap();                         // the host sized the launch so that this cannot happen
   const uint32_t full_a = pl.bars, empty_a = pl.bars + 64, rfull_a = pl.bars + 128, rempty_a = pl.bars + 160;
@@ -185,7 +189,7 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
   if (tid == 0) {
     v4_stamp(p, 0);
     for (int s = 0; s < kV4MaxStages; ++s) { mbar_init(full_a + s * 8, 1); mbar_init(empty_a + s * 8, kV4CW); }
-    for (int s = 0; s < NBUF; ++s) { mbar_init(rfull_a + s * 8, kV4CW); mbar_init(rempty_a + s * 8, 1); }
+    for (int s = 0; s < 4; ++s) { mbar_init(rfull_a + s * 8, kV4CW); mbar_init(rempty_a + s * 8, 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -260,6 +264,11 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
   }
 
   float* red = reinterpret_cast<float*>(sb + pl.red);
+  // float L of the reduction buffers (buffer-major, then warp, then output): plain array, or 32 floats per table-row gap
+  auto red_at = [&](int L) -> float* {
+    if constexpr (GAPRED) return reinterpret_cast<float*>(sb + pl.lut + 128u + (uint32_t)(L >> 5) * 256u + (uint32_t)(L & 31) * 4u);
+    else return red + L;
+  };
 
   if (warp == kV4CW + 1) {
     // ================================ REDUCER WARP ================================================================
@@ -316,14 +325,14 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
         const int w = q / ntl, tl = q - w * ntl;
         const int buf = q % NBUF;
         mbar_wait(rfull_a + buf * 8, (uint32_t)(q / NBUF) & 1u);
-        const float* rb = red + buf * (kV4CW * REDW);
+        const int rb = buf * (kV4CW * REDW);
         float val[2][NV];
 #pragma unroll
         for (int h = 0; h < NV / 4; ++h) {
           float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
           for (int ww = 0; ww < kV4CW; ++ww) {
-            const float4 q4 = *reinterpret_cast<const float4*>(rb + ww * REDW + 128 * h + 4 * lane);
+            const float4 q4 = *reinterpret_cast<const float4*>(red_at(rb + ww * REDW + 128 * h + 4 * lane));
             v.x += q4.x; v.y += q4.y; v.z += q4.z; v.w += q4.w;
           }
           val[1][4 * h] = v.x; val[1][4 * h + 1] = v.y; val[1][4 * h + 2] = v.z; val[1][4 * h + 3] = v.w;
@@ -369,12 +378,12 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
         if (which >= TS || tf < t_first || tf > t_last) continue;
         const int buf = j % NBUF;
         mbar_wait(rfull_a + buf * 8, (uint32_t)(j / NBUF) & 1u);
-        const float* rb = red + buf * (kV4CW * REDW);
+        const int rb = buf * (kV4CW * REDW);
         if constexpr (MODE == 0) {
           const int row = lane & 15, half = lane >> 4;
           float v = 0.f;
 #pragma unroll
-          for (int w = 0; w < kV4CW / 2; ++w) v += rb[(half * (kV4CW / 2) + w) * REDW + row];
+          for (int w = 0; w < kV4CW / 2; ++w) v += red[rb + (half * (kV4CW / 2) + w) * REDW + row];
           v += __shfl_xor_sync(0xffffffffu, v, 16);   // (warps 0..7) + (warps 8..15): same value in both halves
           val[which][0] = v;
         } else {
@@ -383,7 +392,7 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
             for (int w = 0; w < kV4CW; ++w) {
-              const float4 q4 = *reinterpret_cast<const float4*>(rb + w * REDW + 128 * h + 4 * lane);
+              const float4 q4 = *reinterpret_cast<const float4*>(red_at(rb + w * REDW + 128 * h + 4 * lane));
               v.x += q4.x; v.y += q4.y; v.z += q4.z; v.w += q4.w;
             }
             val[which][4 * h] = v.x; val[which][4 * h + 1] = v.y; val[which][4 * h + 2] = v.z; val[which][4 * h + 3] = v.w;
@@ -963,14 +972,14 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
   auto flush = [&]() {   // hand the partial sums of tile `ct` to the reducer (zeros if this warp had no unit of it)
     const int buf = jf % NBUF;
     if (jf >= NBUF) mbar_wait(rempty_a + buf * 8, (uint32_t)((jf / NBUF) - 1) & 1u);
-    float* rbuf = red + buf * (kV4CW * REDW) + warp * REDW;
+    const int rbuf = buf * (kV4CW * REDW) + warp * REDW;
     if constexpr (MODE == 0) {
-      if (t == 0) { rbuf[g] = acc[0][0]; rbuf[g + 8] = acc[0][2]; }
+      if (t == 0) { red[rbuf + g] = acc[0][0]; red[rbuf + g + 8] = acc[0][2]; }
     } else {
 #pragma unroll
       for (int nb = 0; nb < NB; ++nb) {
-        *reinterpret_cast<float2*>(rbuf + g * COLS + 8 * nb + 2 * t) = make_float2(acc[nb][0], acc[nb][1]);
-        *reinterpret_cast<float2*>(rbuf + (g + 8) * COLS + 8 * nb + 2 * t) = make_float2(acc[nb][2], acc[nb][3]);
+        *reinterpret_cast<float2*>(red_at(rbuf + g * COLS + 8 * nb + 2 * t)) = make_float2(acc[nb][0], acc[nb][1]);
+        *reinterpret_cast<float2*>(red_at(rbuf + (g + 8) * COLS + 8 * nb + 2 * t)) = make_float2(acc[nb][2], acc[nb][3]);
       }
     }
 #pragma unroll
@@ -1190,7 +1199,9 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
   const int nrec = int4 ? nkb / 2 : nkb;                 // records per tile
   const int mode = a->batch == 1 ? 0 : (a->batch <= 8 ? 1 : 2);
   const int cols = mode == 2 ? 16 : 8;
-  const int red_bytes = (mode == 0 ? 4 * kV4CW * 16 : 2 * kV4CW * 16 * cols) * 4;
+  const bool gapred = !int4 && mode != 0;                // batched nf4 / fp4: the reduction buffers sit in the table-row gaps
+  int nbuf = mode == 0 ? 4 : 2;
+  int red_bytes = gapred ? 0 : (mode == 0 ? 4 * kV4CW * 16 : nbuf * kV4CW * 16 * cols) * 4;
   const int xstride = (int)a->K + 8;
   const int gap = (!int4 && mode == 0 && nkb <= 256) ? 1 : 0;
   if (!dry && (a->workspace == nullptr || a->workspace_bytes < qgemv_v4_workspace_bytes())) return B200_ERR_UNSUPPORTED;
@@ -1201,6 +1212,15 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
     const int stage = kV4CW * cand * (int4 ? 1088 : 576);
     const V4Plan pl = v4_plan(1024u, stage, red_bytes, int4, a->batch, nkb, xstride, gap, (int4 && mode == 0 && g_v4_occ2.load()) ? kV4DynSmem2 : kV4DynSmem);
     if (pl.S >= 2) { ru = cand; break; }
+  }
+  if (ru == 0 && mode != 0 && !gapred) {
+    // one reduction buffer instead of two when that lets the full activation rows stay resident (no k-windows)
+    const int red1 = kV4CW * 16 * cols * 4;
+    for (int cand = int4 ? 2 : 4; cand >= 1; cand >>= 1) {
+      if (nrec % cand) continue;
+      const V4Plan pl = v4_plan(1024u, kV4CW * cand * (int4 ? 1088 : 576), red1, int4, a->batch, nkb, xstride, gap, kV4DynSmem);
+      if (pl.S >= 2) { ru = cand; nbuf = 1; red_bytes = red1; break; }
+    }
   }
   const int64_t ntiles = (a->N + 15) / 16;
   const int ts = swiglu ? 2 : 1;
@@ -1261,7 +1281,7 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
   p.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual);
   p.y = reinterpret_cast<__nv_bfloat16*>(a->y);
   p.xstride = xstride; p.gap = gap;
-  p.wu = wu; p.nwin = nwin;
+  p.wu = wu; p.nwin = nwin; p.nbuf = nbuf;
   p.att = att; p.att_nsplit = att_nsplit; p.att_tph = att_tph;
   if (att_nsplit) { p.att_cnt = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(a->workspace) + 1024); p.att.fuse_cnt = p.att_cnt; }
   if (nwin > 1) { p.nkb = win_nkb; p.xstride = win_xstride; }
