@@ -100,6 +100,7 @@ class DecodeGraph:
 
     def capture(self) -> None:
         state = (self.token.clone(), self.pos.clone())
+        rng0 = self.rng.clone()   # the warm-up steps below draw from the sampler state: put it back, they are not part of the sequence
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):  # warm-up outside capture: allocates workspaces, sets kernel attributes
@@ -112,6 +113,7 @@ class DecodeGraph:
         with torch.cuda.graph(self.graph):
             self._step()
         self.token.copy_(state[0]); self.pos.copy_(state[1])
+        self.rng.copy_(rng0)
 
     def replay(self) -> None:
         self.graph.replay()

@@ -227,6 +227,13 @@ class GPT(nn.Module):
         return comm or None
 
     # ---- blocks placed on several devices by generate/sequentially.py ----------------------------------------------------
+    def release_reference_layouts(self) -> int:
+        """Keep ONE resident copy of every 4-bit Linear (the tiled layout the decode GEMV streams); see
+        ``QLinear.release_reference_layout``.  Returns the number of Linears whose reference-layout copy was dropped."""
+        n = sum(int(m.release_reference_layout()) for m in self.modules() if isinstance(m, QLinear))
+        self._fused_plan = None
+        return n
+
     def spans_devices(self) -> bool:
         hit = self.__dict__.get("_spans")
         if hit is None:

@@ -325,6 +325,53 @@ def test_tp2_matches_oracle_multi_gpu(mode, inter):
     print(out.stdout[-500:])
 
 
+@pytest.mark.parametrize("mode", ["nf4", "int4", "nf4-dq"])
+@torch.inference_mode()
+def test_single_resident_copy(golden, mode):
+    """`GPT.release_reference_layouts()`: only the tiled copy of every 4-bit Linear stays in HBM (half the bytes); prefill, decode,
+    generate(), dequantize() and state_dict() give exactly what they gave before (the reference layout is rebuilt on the fly by the
+    exact inverse of the tiling)."""
+    import lit_gpt_b200.generate.base as gb
+    from lit_gpt_b200 import QLinear
+
+    g = golden("llama_mha_hs128")
+    cfgd, kw = cfg_from_golden(g)
+    p = M.init_weights(M.RefConfig.from_any(cfgd), seed=21)
+    model = build_cuda_model(kw, p, mode, max_seq=40)
+    prompt = torch.from_numpy(g["gen_prompt"]).cuda()
+    T = prompt.numel()
+
+    def run():
+        for blk in model.transformer.h:
+            blk.attn.kv_cache.reset_parameters()
+        y = model(prompt.view(1, -1), torch.arange(T, device="cuda")).clone()
+        d = model(torch.tensor([[7]], device="cuda"), torch.tensor([T], device="cuda")).clone()
+        for blk in model.transformer.h:
+            blk.attn.kv_cache.reset_parameters()
+        return y, d, gb.generate(model, prompt, 30, temperature=0.0).clone()
+
+    def weight_bytes():
+        n = 0
+        for m in model.modules():
+            if isinstance(m, QLinear):
+                for t in (m.weight.data, m.absmax, m.sz, m.tiled):
+                    n += 0 if t is None else t.numel() * t.element_size()
+        return n
+
+    before = run()
+    sd0 = {k: v.clone() for k, v in model.state_dict().items()}
+    dq0 = model.transformer.h[0].mlp.fc_1.dequantize(torch.float32).clone()
+    b0 = weight_bytes()
+    n = model.release_reference_layouts()
+    assert n == sum(isinstance(m, QLinear) for m in model.modules())
+    assert weight_bytes() <= 0.52 * b0
+    after = run()
+    assert all(torch.equal(a, b) for a, b in zip(before, after))
+    sd1 = model.state_dict()
+    assert sd0.keys() == sd1.keys() and all(torch.equal(sd0[k].view(torch.uint8).flatten(), sd1[k].view(torch.uint8).flatten()) for k in sd0)
+    assert torch.equal(dq0, model.transformer.h[0].mlp.fc_1.dequantize(torch.float32))
+
+
 def _sequential_model(kw, p, mode, devices, max_seq):
     """The load flow of generate/sequentially.py:171-190: weights on the CPU, QLinear modules swapped in, then placed."""
     from lit_gpt_b200 import GPT, Config, QuantPrecision
