@@ -166,9 +166,11 @@ def step_bytes(full_cfg, mode: str, ctx: int, batch: int, tp: int, head_sharded:
     return {"weights": w, "kv": kv, "total": w + kv}
 
 
-def gemv_only_step(model, x, y_attn):
+def gemv_only_step(model, x, y_attn, xn=None):
     """Exactly the dequant-GEMV launches of one fused decode step (norm prologues, residual / SwiGLU epilogues
-    included), without attention / embedding / argmax: used to time the dominant kernel in isolation."""
+    included), without attention / embedding / argmax: used to time the dominant kernel in isolation.
+    xn: the pre-normalised rows for batches above model.SPLIT_NORM_ROWS, where the step runs RMSNorm as its own launch and the
+    GEMVs take plain rows (GPT._fused_decode): the same launches as the step's, the norm launches themselves left out."""
     from lit_gpt_b200 import kernels as K
 
     eps = model.config.norm_eps
@@ -176,20 +178,25 @@ def gemv_only_step(model, x, y_attn):
     def lin(q, inp, nxt=None, **kw):
         return q.gemv(inp, prefetch=None if nxt is None else nxt.tiled, **kw)
 
+    def normed(q, inp, w, nxt=None, **kw):
+        if xn is not None:
+            return lin(q, xn, nxt, **kw)
+        return lin(q, inp, nxt, norm_weight=w, norm_eps=eps, **kw)
+
     blocks = list(model.transformer.h)
     for li, block in enumerate(blocks):
         a, m = block.attn, block.mlp
         nxt_qkv = blocks[li + 1].attn.attn if li + 1 < len(blocks) else model.lm_head
-        lin(a.attn, x, a.proj, norm_weight=block.norm_1.weight, norm_eps=eps)
+        normed(a.attn, x, block.norm_1.weight, a.proj)
         if model.tp_world_size > 1:
             h = lin(a.proj, y_attn, m.fc_1)
             act = lin(m.fc_1, x, m.proj, other=m.fc_2, delta=h, norm_weight=block.norm_2.weight, norm_eps=eps)
             lin(m.proj, act, nxt_qkv)
         else:
             x2 = lin(a.proj, y_attn, m.fc_1, residual=x)
-            act = lin(m.fc_1, x2, m.proj, other=m.fc_2, norm_weight=block.norm_2.weight, norm_eps=eps)
+            act = normed(m.fc_1, x2, block.norm_2.weight, m.proj, other=m.fc_2)
             lin(m.proj, act, nxt_qkv, residual=x2)
-    lin(model.lm_head, x, blocks[0].attn.attn, norm_weight=model.transformer.ln_f.weight, norm_eps=eps)
+    normed(model.lm_head, x, model.transformer.ln_f.weight, blocks[0].attn.attn)
 
 
 def time_graph(graph, n: int, world: int) -> float:
@@ -368,12 +375,16 @@ def run_ours(args) -> None:
     # ---- dominant kernel in isolation: the dequant-GEMV launches of one step, same weights (3.7 GB >> L2) ----
     x = torch.randn(batch, model.transformer.wte.weight.shape[1], device=dev).to(torch.bfloat16)
     y_attn = torch.randn(batch, model.transformer.h[0].attn.proj.in_features, device=dev).to(torch.bfloat16)
+    from lit_gpt_b200.model import SPLIT_NORM_ROWS
+
+    split_norm = batch > SPLIT_NORM_ROWS and world == 1   # the step then normalises in its own launch and the GEMVs take plain rows
+    xn = K.rmsnorm(x, model.transformer.ln_f.weight, model.config.norm_eps) if split_norm else None
     n0 = K.launch_count()
-    gemv_only_step(model, x, y_attn)
+    gemv_only_step(model, x, y_attn, xn)
     gemv_launches = K.launch_count() - n0
     gg = torch.cuda.CUDAGraph()
     with torch.cuda.graph(gg):
-        gemv_only_step(model, x, y_attn)
+        gemv_only_step(model, x, y_attn, xn)
     time_graph(gg, W, 1)
     reps = max(8, min(K_steps, 64))
     gemv_ms = time_graph(gg, reps, 1) / reps
@@ -389,7 +400,8 @@ def run_ours(args) -> None:
         tj = json.load(open(tpath))
         if tj.get("workload") == args.workload and world == 1:
             traffic = tj["traffic_over_algorithmic"] * bytes_step["weights"] / max(1, gemv_launches)
-    roofline = {"bound": "hbm", "kernel": "qgemv_v4_kernel", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+    kernel_name = "qgemv_v4_kernel" if batch == 1 or world > 1 else ("qgemv_nb_kernel" if split_norm else "qgemv_v4_kernel (norm-fused launches) + qgemv_nb_kernel (plain rows)")
+    roofline = {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": achieved / peaks["hbm_gbs"], "traffic": traffic,
                 "traffic_source": None if traffic is None else "constant: ncu dram__bytes_read+write of the committed capture (profiles/), "
                                                                 "scaled by this run's algorithmic bytes; not measured by this run",

@@ -556,6 +556,7 @@ __global__ void __launch_bounds__(kSThreadsAll, 1) qgemv_stream_kernel(const Str
   }
 }
 
+static std::atomic<int> g_nb_min_batch{2};   // plain rows from this batch on run the tile-per-warp kernel (qgemv_nb.cu); 17 = never
 static std::atomic<int> g_stream_depth{0}, g_stream_occ{0}, g_stream_pf{0};  // L2 prefetch of the next launch's weights: off by default (no measured gain, extra DRAM traffic when lines are evicted before use)
 
 template <int NB, bool INT4>
@@ -575,7 +576,7 @@ using namespace b200;
 
 extern "C" {
 
-size_t b200_qgemv_tiled_workspace_bytes(void) { return qgemv_v4_workspace_bytes(); }  // stream-K partial sums + flags (self-cleaning)
+size_t b200_qgemv_tiled_workspace_bytes(void) { return qgemv_v4_workspace_bytes() + qgemv_nb_workspace_bytes(); }  // stream-K partial sums + flags (self-cleaning)
 
 int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch) {
   g_stream_depth = depth;
@@ -583,6 +584,8 @@ int b200_qgemv_tiled_tune(int depth, int ctas_per_sm, int l2_prefetch) {
   // development knobs: 10 = never split entities, 11 = always, 12 = no register-resident activations
   qgemv_v4_tune(ctas_per_sm == 11 ? 1 : ctas_per_sm == 10 ? 0 : -1, ctas_per_sm == 12 ? 0 : 1);
   qgemv_v4_tune_occ2(ctas_per_sm == 13 ? 1 : 0);
+  qgemv_nb_tune_ru(ctas_per_sm >= 41 && ctas_per_sm <= 44 ? ctas_per_sm - 40 : 4);   // 41 / 42: at most 1 / 2 records per step and tile
+  g_nb_min_batch = (ctas_per_sm >= 22 && ctas_per_sm <= 37) ? ctas_per_sm - 20 : 2;   // 22..36: batched kernel from 2..16 rows on, 37: off
   qgemv_v4_tune_kvhint(ctas_per_sm == 14 ? 0 : 1);   // 14: ignore the K / V cache L2 hint   // 13: int4 batch-1 as two co-resident CTAs per SM (experiment)
   g_stream_pf = l2_prefetch;
   return B200_OK;
@@ -631,6 +634,15 @@ static int qgemv_tiled_impl(const b200_qgemv_tiled_args* a, b200_stream_t stream
       B200_CHECK_ARG(h->recv_seq && h->recv_done && h->slot_stride >= (int64_t)a->batch * a->K * 4 && h->slot_stride % 16 == 0 &&
                          (reinterpret_cast<uintptr_t>(h->slots) & 15) == 0,
                      "b200_qgemv_tiled: tp consumer needs recv_seq, recv_done and 16-byte aligned slots of >= batch * K * 4 bytes");
+  }
+  // more than one PLAIN row (no norm / delta prologue, no tensor-parallel hand-off): one row tile per warp (qgemv_nb.cu)
+  if (a->batch >= g_nb_min_batch.load() && (g_stream_depth.load() == 0 || g_stream_depth.load() == 99)) {
+    const bool ws_ok = dry || (a->workspace && a->workspace_bytes >= qgemv_v4_workspace_bytes() + qgemv_nb_workspace_bytes());
+    if (ws_ok) {
+      uint8_t* ws = dry ? nullptr : reinterpret_cast<uint8_t*>(a->workspace) + qgemv_v4_workspace_bytes();
+      const int rc = qgemv_nb_launch(a, ws, dry ? nullptr : qgemv_v4_take_trace_slot(), (cudaStream_t)stream, dry, g_stream_depth.load() == 99 ? 1 : 0);
+      if (rc != B200_ERR_UNSUPPORTED) return rc;
+    }
   }
   // stream-K kernel (qgemv_v4.cu) unless forced off (tune depth 98) or the shape is outside its plan
   if (g_stream_depth.load() != 98) {

@@ -190,6 +190,7 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
     v4_stamp(p, 0);
     for (int s = 0; s < kV4MaxStages; ++s) { mbar_init(full_a + s * 8, 1); mbar_init(empty_a + s * 8, kV4CW); }
     for (int s = 0; s < 4; ++s) { mbar_init(rfull_a + s * 8, kV4CW); mbar_init(rempty_a + s * 8, 1); }
+    mbar_init(pl.bars + 192, 1);   // activation rows copied by cp.async.bulk (batch > 1 without norm / delta)
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -276,19 +277,25 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
     griddep_wait();
     uint32_t* wsflag = reinterpret_cast<uint32_t*>(p.ws + 64);
     const uint32_t stag = p.tp_send_seq ? (__ldcg(p.tp_send_seq) % 65535u) + 1u : 0u;
-    auto store_out = [&](int64_t n, int c, float v) {  // STORE / RESIDUAL epilogues for one (row, batch column)
+    // STORE / RESIDUAL epilogues for one (row, batch column): `addend` = bias (+ nothing) and `res` = the residual value, both
+    // loaded by the caller for ALL of a lane's outputs before the first store (y may alias residual, so the compiler cannot
+    // hoist them itself: eight dependent L2 round trips per tile made the reducer the longest warp of a batched launch)
+    auto out_index = [&](int64_t& n, int& c) {
       if (p.fold > 1) {  // folded view: row n holds the true rows n * fold + h, column c = batch row * fold + h
         n = n * p.fold + (c % p.fold);
         c /= p.fold;
       }
-      float h = v + (p.bias ? __bfloat162float(p.bias[n]) : 0.f);
-      if (p.epilogue == B200_EPI_RESIDUAL) h = round_bf16(h) + __bfloat162float(p.residual[(int64_t)c * p.Nout + n]);
+      return (int64_t)c * p.Nout + n;
+    };
+    auto store_at = [&](int64_t at, float v, float addend, float res) {
+      float h = v + addend;
+      if (p.epilogue == B200_EPI_RESIDUAL) h = round_bf16(h) + res;
       const __nv_bfloat16 hb = __float2bfloat16_rn(h);
-      if (p.y) p.y[(int64_t)c * p.Nout + n] = hb;
+      if (p.y) p.y[at] = hb;
       if (p.tp_send_seq) {  // row-parallel partial: one self-validating packet straight into every rank's slot over NVLink
         const uint32_t pk = (stag << 16) | (uint32_t)bf16_bits(h);
         for (int r = 0; r < p.tp_world; ++r)
-          asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p.tp_peer_y[r] + (int64_t)c * p.Nout + n), "r"(pk) : "memory");
+          asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p.tp_peer_y[r] + at), "r"(pk) : "memory");
       }
     };
     // epilogue of a complete entity (tile, or gate tile + up tile): bias / residual / SwiGLU / tensor-parallel packets
@@ -306,12 +313,24 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
         }
       }
     } else {
+      int64_t at[NV];
+      float addend[NV], res[NV];
 #pragma unroll
       for (int i = 0; i < NV; ++i) {
         const int o = MODE == 0 ? lane : 4 * lane + (i & 3) + 128 * (i >> 2);   // batch > 1: lane owns four consecutive outputs per 128
-        const int row = MODE == 0 ? (lane & 15) : o / COLS, c = MODE == 0 ? 0 : o % COLS;
-        const int64_t nrow = (int64_t)e * 16 + row;
-        if ((MODE != 0 || lane < 16) && c < B && nrow < p.N) store_out(nrow, c, val[0][i]);
+        const int row = MODE == 0 ? (lane & 15) : o / COLS;
+        int c = MODE == 0 ? 0 : o % COLS;
+        int64_t nrow = (int64_t)e * 16 + row;
+        const bool ok = (MODE != 0 || lane < 16) && c < B && nrow < p.N;
+        at[i] = ok ? out_index(nrow, c) : -1;
+        addend[i] = ok && p.bias ? __bfloat162float(p.bias[nrow]) : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < NV; ++i)
+        res[i] = at[i] >= 0 && p.epilogue == B200_EPI_RESIDUAL ? __bfloat162float(p.residual[at[i]]) : 0.f;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        if (at[i] >= 0) store_at(at[i], val[0][i], addend[i], res[i]);
       }
     }
       };
@@ -520,6 +539,15 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
     const int k0 = w * p.wu * UK;
     const int kw = min(p.wu * UK, (int)p.K - k0), wch = kw >> 3;
     const int total = B * wch;                 // 16-byte chunks of the window, all rows: four loads in flight per thread
+    if (!p.norm_w && !p.delta) {
+      // plain rows (the 16-token prompt prefill, row-parallel Linears): one bulk copy per row, no per-element instructions
+      if (tid == 0) {
+        mbar_expect_tx(pl.bars + 192, (uint32_t)(B * kw * 2));
+        for (int b = 0; b < B; ++b)
+          bulk_g2s_plain(pl.xs + (uint32_t)(b * p.xstride) * 2u, p.x + (int64_t)b * p.K + k0, (uint32_t)(kw * 2), pl.bars + 192);
+      }
+      mbar_wait(pl.bars + 192, (uint32_t)w & 1u);
+    } else {
     for (int i0 = tid; i0 < total; i0 += 4 * kV4Consumers) {
       uint4 v[4], dv[4], nw[4];
       int bb[4], cc[4];
@@ -551,6 +579,7 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
       }
     }
     asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
+    }
     if (INT4) {   // per (row, k-block of the window) activation sums for the zero-point term (blocks past a short last window: unused)
       xsum_blocks<kV4Consumers>(reinterpret_cast<const __nv_bfloat16*>(sb + pl.xs), p.xstride, B, p.nkb, xsum_s, tid);
       asm volatile("bar.sync 1, %0;" ::"n"(kV4Consumers) : "memory");
@@ -673,7 +702,15 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
     }
     if (tid == 0 && p.debug == 3) v4_stamp_cyc(p, 7, c_rel);
   } else {
-    if (!p.tp_slots && p.fold <= 1) {
+    if (!p.tp_slots && p.fold <= 1 && !p.norm_w && !p.delta && !p.gap) {
+      // batch > 1, plain rows: one bulk copy per row straight into shared memory (no per-element instructions)
+      if (tid == 0) {
+        mbar_expect_tx(pl.bars + 192, (uint32_t)(B * (int)p.K * 2));
+        for (int b = 0; b < B; ++b)
+          bulk_g2s_plain(pl.xs + (uint32_t)(b * p.xstride) * 2u, p.x + (int64_t)b * p.K, (uint32_t)((int)p.K * 2), pl.bars + 192);
+      }
+      mbar_wait(pl.bars + 192, 0u);
+    } else if (!p.tp_slots && p.fold <= 1) {
       // batch > 1: the (row, chunk) items of this thread in row-major order, four global loads in flight at a time (a plain
       // row loop serialises one L2 round trip per row: the shared-memory stores in between keep ptxas from hoisting loads)
       const int ncm = (chunks + kV4Consumers - 1) / kV4Consumers, items = B * ncm;
@@ -1105,6 +1142,9 @@ __global__ void __launch_bounds__(kV4Threads, OCC) qgemv_v4_kernel(const V4Param
 
 static unsigned long long* g_v4_trace = nullptr;   // development: device buffer [slots][kV4MaxCtas][8]
 static int g_v4_trace_slots = 0, g_v4_trace_next = 0;
+unsigned long long* qgemv_v4_take_trace_slot() {
+  return (g_v4_trace && g_v4_trace_next < g_v4_trace_slots) ? g_v4_trace + (size_t)(g_v4_trace_next++) * kV4MaxCtas * 8 : nullptr;
+}
 void qgemv_v4_set_trace(void* buf, int slots) { g_v4_trace = reinterpret_cast<unsigned long long*>(buf); g_v4_trace_slots = slots; g_v4_trace_next = 0; }
 
 static std::atomic<int> g_v4_occ2{0};     // experiment: int4 batch-1 launches as two co-resident CTAs per SM
@@ -1307,7 +1347,7 @@ int qgemv_v4_launch(const b200_qgemv_tiled_args* a0, int debug, cudaStream_t st,
       p.tp_reduced = reinterpret_cast<uint32_t*>(h->reduced);
     }
   }
-  if (g_v4_trace && g_v4_trace_next < g_v4_trace_slots) p.trace = g_v4_trace + (size_t)(g_v4_trace_next++) * kV4MaxCtas * 8;
+  p.trace = qgemv_v4_take_trace_slot();
   int gx = sm_count();
   if (gx > kV4MaxCtas) gx = kV4MaxCtas;
   // Whole entities per CTA unless the resulting imbalance costs more than the partial hand-off of a split entity

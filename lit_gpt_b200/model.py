@@ -25,6 +25,9 @@ from . import kernels as K
 from .config import Config
 from .quant import QLinear
 
+# batched decode with more rows than this runs RMSNorm as its own launch instead of in the GEMV prologue (see GPT._fused_decode)
+SPLIT_NORM_ROWS = int(__import__("os").environ.get("B200_SPLIT_NORM_ROWS", "8"))
+
 FUSED_HEAD_SIZES = (64, 128)
 
 
@@ -343,15 +346,24 @@ class GPT(nn.Module):
                     x = x.to(dev, non_blocking=True)
                 cos, sin = self._tables_on(dev)
                 pos = input_pos if input_pos.device == dev else input_pos.to(dev, non_blocking=True)
-                qkv = a.attn.gemv(x, norm_weight=block.norm_1.weight, norm_eps=eps, kv_hint=(cache.k, cache.v, pos))
+                if B > SPLIT_NORM_ROWS:   # see _fused_decode
+                    qkv = a.attn.gemv(K.rmsnorm(x, block.norm_1.weight, eps), kv_hint=(cache.k, cache.v, pos))
+                else:
+                    qkv = a.attn.gemv(x, norm_weight=block.norm_1.weight, norm_eps=eps, kv_hint=(cache.k, cache.v, pos))
                 y = K.attn_decode(qkv, cos, sin, pos, cache.k, cache.v, c.n_head, c.n_query_groups, c.head_size, c.rope_n_elem)
                 x = a.proj.gemv(y, residual=x)
-                act = m.fc_1.gemv(x, other=m.fc_2, norm_weight=block.norm_2.weight, norm_eps=eps)
+                if B > SPLIT_NORM_ROWS:
+                    act = m.fc_1.gemv(K.rmsnorm(x, block.norm_2.weight, eps), other=m.fc_2)
+                else:
+                    act = m.fc_1.gemv(x, other=m.fc_2, norm_weight=block.norm_2.weight, norm_eps=eps)
                 x = m.proj.gemv(act, residual=x)
         with torch.cuda.device(root):
             if x.device != root:
                 x = x.to(root, non_blocking=True)
-            logits = self.lm_head.gemv(x, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+            if B > SPLIT_NORM_ROWS:
+                logits = self.lm_head.gemv(K.rmsnorm(x, self.transformer.ln_f.weight, eps))
+            else:
+                logits = self.lm_head.gemv(x, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
         return logits.view(B, 1, -1)
 
     def _gather_dummy(self, B: int, n: int, device: torch.device) -> torch.Tensor:
@@ -444,6 +456,9 @@ class GPT(nn.Module):
                      and a0.fold == 1 and a0.streams(1) and input_pos.numel() == 1
                      and K.qgemv_attn_fusable(a0.out_features, a0.in_features, a0.quant_type, c.n_head, c.n_query_groups, c.head_size,
                                               c.rope_n_elem, self.max_seq_length))
+        # more than 8 rows: RMSNorm as its own launch.  Fused, EVERY CTA of the GEMV normalises all the rows again (148 x redundant:
+        # at 16 rows two thirds of the launch's instructions); plain rows reach shared memory by one bulk copy each
+        split_norm = B > SPLIT_NORM_ROWS and not tp
         for li, block in enumerate(blocks):
             a, m, cache = block.attn, block.mlp, block.attn.kv_cache
             nxt_qkv = blocks[li + 1].attn.attn if li + 1 < len(blocks) else self.lm_head
@@ -458,6 +473,8 @@ class GPT(nn.Module):
                 x_new = torch.empty_like(x)
                 qkv = lin(a.attn, x, a.proj, delta=delta, x_out=x_new, norm_weight=block.norm_1.weight, norm_eps=eps, kv_hint=hint)
                 x = x_new
+            elif split_norm:
+                qkv = lin(a.attn, K.rmsnorm(x, block.norm_1.weight, eps), a.proj, kv_hint=hint)
             else:
                 qkv = lin(a.attn, x, a.proj, norm_weight=block.norm_1.weight, norm_eps=eps, kv_hint=hint)
             if not fuse_attn:
@@ -471,10 +488,16 @@ class GPT(nn.Module):
                 delta = self._all_reduce(lin(m.proj, act, nxt_qkv))
             else:
                 x = lin(a.proj, y, m.fc_1, residual=x)
-                act = lin(m.fc_1, x, m.proj, other=m.fc_2, norm_weight=block.norm_2.weight, norm_eps=eps)
+                if split_norm:
+                    act = lin(m.fc_1, K.rmsnorm(x, block.norm_2.weight, eps), m.proj, other=m.fc_2)
+                else:
+                    act = lin(m.fc_1, x, m.proj, other=m.fc_2, norm_weight=block.norm_2.weight, norm_eps=eps)
                 x = lin(m.proj, act, nxt_qkv, residual=x)
         first = blocks[0].attn.attn if blocks else None  # graph replays run back to back: wrap the prefetch around
-        logits = lin(self.lm_head, x, first, delta=delta, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
+        if split_norm:
+            logits = lin(self.lm_head, K.rmsnorm(x, self.transformer.ln_f.weight, eps), first)
+        else:
+            logits = lin(self.lm_head, x, first, delta=delta, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
         if tp and getattr(self, "lm_head_sharded", False):   # all-NCCL tensor-parallel path (B200_TP_NCCL=1): gather the vocabulary slices
             import torch.distributed as dist
 

@@ -201,6 +201,67 @@ def test_qgemv_tiled_k_windows_swiglu(K, qt):
     assert e_k <= 2.0 * e_t + 2 ** -8 * wide.abs().max().item(), (e_k, e_t)
 
 
+@pytest.mark.parametrize("qt", ["nf4", "fp4", "int4"])
+@pytest.mark.parametrize("N,Kdim,B", [(4096, 11008, 16), (5120, 13824, 16), (4096, 4096, 9), (12288, 4096, 16), (1000, 5120, 5), (48, 28672, 2),
+                                      (32000, 1024, 16), (4096, 128, 12), (16, 256, 16), (4112, 2048, 7)])
+def test_qgemv_batched_tile_per_warp(K, qt, N, Kdim, B):
+    """csrc/qgemv_nb.cu: 2..16 PLAIN rows, one 16-row tile per warp, the activation slice streamed with the weights, groups of 16
+    tiles cut by a stream-K boundary summed in CTA order through self-validating words in the workspace.  Shapes: many
+    contributors per group (4096 x 11008, 5120 x 13824: ~9 CTAs per group), whole groups per CTA (32000 x 1024), a single step per
+    tile (K = 128 / 256), partial last groups (1000, 48, 16, 4112 rows), every batch parity.  Checked against the oracle's
+    dequantised weights, against the k-split kernel (qgemv_v4.cu, forced with the tuning switch) and for run-to-run equality
+    (deterministic order, workspace left clean); RESIDUAL in place (y aliases residual), bias, SwiGLU pair."""
+    if qt == "fp4" and (N, Kdim, B) not in ((4096, 4096, 9), (1000, 5120, 5)):
+        pytest.skip("fp4 shares the nf4 path: sampled subset")
+    w, x, packed, scale, bs, deq = _gemv_case(K, N, Kdim, B, qt, seed=N + Kdim + B)
+    tiled = K.tile_4bit(packed, scale, N, Kdim, qt, bs)
+    xd = x.cuda()
+    n0 = K.launch_count()
+    y = K.qgemv_tiled(xd, tiled, N, Kdim, qt, bs)
+    assert K.launch_count() == n0 + 1
+    _check_gemv(y, x.float(), deq)
+    # a different shape in between (its cut groups use the same workspace words), then the same launch again
+    w_b, x_b, p_b, s_b, _, deq_b = _gemv_case(K, 4096, 2048, 16, qt, seed=1)
+    _check_gemv(K.qgemv_tiled(x_b.cuda(), K.tile_4bit(p_b, s_b, 4096, 2048, qt, bs), 4096, 2048, qt, bs), x_b.float(), deq_b)
+    assert torch.equal(y, K.qgemv_tiled(xd, tiled, N, Kdim, qt, bs)), "not deterministic / workspace not left clean"
+    try:   # the k-split kernel on the same arguments: same operands, another summation order
+        K.qgemv_tiled_tune(0, 37, True)
+        y_v4 = K.qgemv_tiled(xd, tiled, N, Kdim, qt, bs)
+    finally:
+        K.qgemv_tiled_tune(0, 0, True)
+    assert (y.float() - y_v4.float()).abs().max() <= 2 ** -6 * max(1e-3, y_v4.float().abs().max().item())
+    # RESIDUAL epilogue in place + bias (model.py:591: x = attn(...) + x)
+    bias, res = _randw((N,), 7, std=0.5), _randw((B, N), 8, std=1.0)
+    buf = res.cuda().clone()
+    out = K.qgemv_tiled(xd, tiled, N, Kdim, qt, bs, bias=bias.cuda(), residual=buf, out=buf)
+    assert out.data_ptr() == buf.data_ptr()
+    _check_gemv(out, x.float(), deq, post=lambda t: (t + bias.float()).to(torch.bfloat16).float() + res.float())
+    K.check_gemv_errors(torch.device("cuda", 0))
+
+
+@pytest.mark.parametrize("qt", ["nf4", "int4"])
+@pytest.mark.parametrize("N,Kdim,B", [(13824, 5120, 16), (1376, 4096, 2), (344, 1024, 11)])
+def test_qgemv_batched_tile_per_warp_swiglu(K, qt, N, Kdim, B):
+    """The SwiGLU pair on the batched kernel: gate and up tiles alternate over the warps of a group, the up warp hands its
+    rounded values to the gate warp through shared memory (model.py:712-716 rounding points)."""
+    w1, x, p1, s1, bs, d1 = _gemv_case(K, N, Kdim, B, qt, seed=21)
+    w2, _, p2, s2, _, d2 = _gemv_case(K, N, Kdim, B, qt, seed=22)
+    t1, t2 = K.tile_4bit(p1, s1, N, Kdim, qt, bs), K.tile_4bit(p2, s2, N, Kdim, qt, bs)
+    b1, b2 = _randw((N,), 23, std=0.5), _randw((N,), 24, std=0.5)
+    for bias in (False, True):
+        kw = dict(bias=b1.cuda(), bias2=b2.cuda()) if bias else {}
+        y = K.qgemv_tiled(x.cuda(), t1, N, Kdim, qt, bs, tiled2=t2, **kw).float().cpu()
+        xb = x.to(torch.bfloat16).cuda()
+        a = torch.nn.functional.linear(xb, d1.to(torch.bfloat16).cuda(), b1.cuda() if bias else None)
+        b = torch.nn.functional.linear(xb, d2.to(torch.bfloat16).cuda(), b2.cuda() if bias else None)
+        comp = (torch.nn.functional.silu(a) * b).float().cpu()
+        za, zb = x.double() @ d1.double().T + (b1.double() if bias else 0), x.double() @ d2.double().T + (b2.double() if bias else 0)
+        wide = (torch.nn.functional.silu(za) * zb).float()
+        e_k, e_t = (y - wide).abs().max().item(), (comp - wide).abs().max().item()
+        assert e_k <= 2.0 * e_t + 2 ** -8 * wide.abs().max().item(), (bias, e_k, e_t)
+        assert torch.equal(y, K.qgemv_tiled(x.cuda(), t1, N, Kdim, qt, bs, tiled2=t2, **kw).float().cpu())
+
+
 @pytest.mark.parametrize("qt", ["nf4", "fp4"])
 @pytest.mark.parametrize("N,Kdim,B,fold", [(4096, 1376, 1, 2), (256, 96, 3, 2), (512, 1376, 8, 2), (64, 48, 2, 4), (4096, 1376, 4, 2)])
 def test_qgemv_tiled_folded_rows(K, qt, N, Kdim, B, fold):

@@ -35,6 +35,7 @@ def main() -> None:
     ap.add_argument("--depth", type=int, default=0)
     ap.add_argument("--l2pf", type=int, default=1)
     ap.add_argument("--tiny", action="store_true")
+    ap.add_argument("--only", default="", help="substring of the shape names to run (profiling)")
     args = ap.parse_args()
 
     from lit_gpt_b200 import Config
@@ -47,6 +48,8 @@ def main() -> None:
               ("mlp.proj+res", d, I, "res"), ("lm_head+norm", V, d, "norm")]
     if args.tiny:  # one tile per SM: the time of such a launch is the fixed cost of a kernel boundary
         shapes += [("tiny+norm", 148 * 16, d, "norm"), ("tiny+res", 148 * 16, d, "res")]
+    if args.only:
+        shapes = [s for s in shapes if args.only in s[0]]
     dev = torch.device("cuda")
     K.set_pdl(bool(args.pdl))
     K.qgemv_tune(args.ks, args.occ)
@@ -130,6 +133,9 @@ def main() -> None:
             print(row, flush=True)
         del mats
         torch.cuda.empty_cache()
+    if args.only:
+        print(json.dumps(rows), flush=True)
+        return
     per_layer = sum(r["chain_us"] for r in rows[:4])
     summary = {"model": args.model, "qt": args.qt, "batch": args.batch, "kernel": args.kernel, "depth": args.depth, "l2pf": args.l2pf, "ks": args.ks, "occ": args.occ, "pdl": args.pdl,
                "per_layer_us": round(per_layer, 2), "step_est_us": round(per_layer * c.n_layer + rows[4]["chain_us"], 1), "rows": rows}

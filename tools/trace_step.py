@@ -22,6 +22,8 @@ def main() -> None:
     ap.add_argument("--qt", default="nf4")
     ap.add_argument("--layers", type=int, default=4)
     ap.add_argument("--ctx", type=int, default=256)
+    ap.add_argument("--batch", type=int, default=1)
+    ap.add_argument("--dump", type=int, default=-1, help="launch slot whose slowest and fastest CTAs are listed stamp by stamp")
     ap.add_argument("--prologue", action="store_true", help="cycle stamps inside the prologue instead of the stream phases")
     args = ap.parse_args()
     import bench
@@ -29,12 +31,12 @@ def main() -> None:
     from lit_gpt_b200.fabric import Fabric
 
     fabric = Fabric(devices=1, plugins=QuantPrecision(args.qt, torch.bfloat16))
-    model, _ = bench.build_random_model(args.model, args.qt, args.ctx + 32, 1, fabric, n_layer=args.layers)
+    model, _ = bench.build_random_model(args.model, args.qt, args.ctx + 32, args.batch, fabric, n_layer=args.layers)
     dev = fabric.device
-    tok = torch.tensor([[7]], device=dev)
+    tok = torch.full((args.batch, 1), 7, device=dev)
     pos = torch.tensor([args.ctx], device=dev)
     with torch.inference_mode():
-        model(torch.randint(0, 1000, (1, 16), device=dev), torch.arange(16, device=dev))
+        model(torch.randint(0, 1000, (args.batch, 16), device=dev), torch.arange(16, device=dev))
         for _ in range(3):
             model(tok, pos)
         torch.cuda.synchronize()
@@ -60,6 +62,16 @@ def main() -> None:
         print(f"step {e0.elapsed_time(e1) / 20 * 1e3:.1f} us for {args.layers} layers + lm_head")
     t = buf.cpu().numpy().reshape(slots, 160, 8).astype(np.float64)
     names = ["qkv", "proj", "fc", "mproj"]
+    if args.dump >= 0:
+        a = t[args.dump]
+        used = a[:, 0] > 0
+        t0 = a[used][:, 0].min()
+        order = np.argsort(np.where(used, a[:, 5], 0))
+        order = [i for i in order if used[i]]
+        print("cta | entry dep-release prologue-end 1st-stage last-consumed done producer-done gather-start")
+        for i in sorted(order):
+            r = a[i] - t0
+            print(f"{i:4d} | {r[0]:6.0f} {r[1]:6.0f} {r[2]:6.0f} {r[3]:6.0f} {r[4]:6.0f} {r[5]:6.0f} {r[6]:6.0f} {r[7]:6.0f}")
     if args.prologue:
         print("cycles after the dependency release (median over CTAs): x loaded+ssq | 1st barrier | scaled | prologue end (ns) | first stage passed")
         for s in range(slots):
