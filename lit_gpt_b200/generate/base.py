@@ -119,11 +119,66 @@ class DecodeGraph:
         self.graph.replay()
 
 
-def _decode_graph_for(model: GPT, temperature: float, top_k: Optional[int], dtype: torch.dtype) -> DecodeGraph:
-    cache: Dict[Tuple, DecodeGraph] = model.__dict__.setdefault("_decode_graphs", {})
+PREFILL_GRAPH_MAX_T = 16   # prompts up to this length run their prefill as one captured graph (0 switches it off)
+
+
+class PrefillGraph:
+    """The prefill of a SHORT prompt (T <= 16 rows: every Linear is a batched GEMV launch) plus the first draw, captured once per
+    prompt length.  Run eagerly that prefill is host-bound: ~300 launches at ~17 us of Python / ctypes each (5 - 6 ms for a 7B
+    model) against ~2 ms on the device; `generate/base.py`'s sample loop and a served short prompt repeat the same length.  The
+    first call with a new length pays the capture (two warm-up runs + the capture, ~3 x an eager prefill)."""
+
+    def __init__(self, model: GPT, T: int, temperature: float, top_k: Optional[int], dtype: torch.dtype) -> None:
+        dev = model.transformer.wte.weight.device
+        self.model, self.temperature, self.top_k = model, temperature, top_k
+        self.prompt = torch.zeros(1, T, dtype=dtype, device=dev)
+        self.pos = torch.arange(0, T, device=dev)
+        self.token: Optional[torch.Tensor] = None
+        self.rng = _rng_for(dev)
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+
+    def _run(self) -> None:
+        self.token = next_token(self.model, self.pos, self.prompt, temperature=self.temperature, top_k=self.top_k)
+
+    def capture(self) -> None:
+        rng0 = self.rng.clone()   # the warm-up runs draw from the sampler state: put it back (DecodeGraph.capture)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self._run()
+        torch.cuda.current_stream().wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._run()
+        self.rng.copy_(rng0)
+
+
+def _graph_key(model: GPT) -> Tuple:
     # a captured graph bakes in raw device pointers: key on the addresses themselves (id() of a freed tensor can be reused)
     kv = [(b.attn.kv_cache.k.data_ptr(), b.attn.kv_cache.v.data_ptr()) for b in model.transformer.h]
-    key = (temperature, top_k, dtype, model.max_seq_length, tuple(kv), model.cos.data_ptr(), model.sin.data_ptr(), weight_epoch())
+    dev = model.transformer.wte.weight.device
+    rng = _rng_for(dev).data_ptr() if dev.type == "cuda" else 0   # the sampler state's address is baked in too
+    return (model.max_seq_length, tuple(kv), model.cos.data_ptr(), model.sin.data_ptr(), weight_epoch(), rng)
+
+
+def _prefill_graph_for(model: GPT, T: int, temperature: float, top_k: Optional[int], dtype: torch.dtype) -> PrefillGraph:
+    cache: Dict[Tuple, PrefillGraph] = model.__dict__.setdefault("_prefill_graphs", {})
+    key = (T, temperature, top_k, dtype) + _graph_key(model)
+    pg = cache.get(key)
+    if pg is None:
+        if cache and next(iter(cache))[4:] != key[4:]:
+            cache.clear()  # buffers or weights changed: the old graphs pin stale addresses
+        if len(cache) >= 2 * PREFILL_GRAPH_MAX_T:
+            cache.pop(next(iter(cache)))
+        pg = PrefillGraph(model, T, temperature, top_k, dtype)
+        cache[key] = pg
+    return pg
+
+
+def _decode_graph_for(model: GPT, temperature: float, top_k: Optional[int], dtype: torch.dtype) -> DecodeGraph:
+    cache: Dict[Tuple, DecodeGraph] = model.__dict__.setdefault("_decode_graphs", {})
+    key = (temperature, top_k, dtype) + _graph_key(model)
     dg = cache.get(key)
     if dg is None:
         cache.clear()  # graphs pin the kv-cache buffers they were captured with
@@ -148,9 +203,18 @@ def generate(model: GPT, prompt: torch.Tensor, max_returned_tokens: int, *, temp
         _rng_for(device)   # apply a pending reseed before any draw of this call
     tokens = [prompt]
     input_pos = torch.tensor([T], device=device)
-    token = next_token(
-        model, torch.arange(0, T, device=device), prompt.view(1, -1), temperature=temperature, top_k=top_k
-    ).clone()
+    if (1 < T <= PREFILL_GRAPH_MAX_T and prompt.is_cuda and getattr(model, "tp_world_size", 1) == 1 and not model.spans_devices()
+            and model.fused_decode_ready(prompt.view(1, -1)) and model.config.intermediate_size % 8 == 0):
+        pg = _prefill_graph_for(model, T, temperature, top_k, prompt.dtype)
+        pg.prompt.copy_(prompt.view(1, -1))
+        if pg.graph is None:
+            pg.capture()
+        pg.graph.replay()
+        token = pg.token.clone()
+    else:
+        token = next_token(
+            model, torch.arange(0, T, device=device), prompt.view(1, -1), temperature=temperature, top_k=top_k
+        ).clone()
     tokens.append(token)
     n_steps = max_returned_tokens - T - 1
 

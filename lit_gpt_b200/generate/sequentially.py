@@ -76,6 +76,7 @@ def sequential(model: GPT, root: torch.device, max_seq_length: int, devices: int
     replace_device(model, replace=torch.device("cpu"), by=root)
     model._fused_plan = None
     model.__dict__.pop("_decode_graphs", None)
+    model.__dict__.pop("_prefill_graphs", None)
     model.__dict__.pop("_seq_tables", None)
     model.__dict__.pop("_spans", None)
 

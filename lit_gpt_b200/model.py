@@ -132,6 +132,7 @@ class GPT(nn.Module):
             self.mask_cache = build_mask_cache(max_seq_length, device)
         self._fused_plan = None
         self.__dict__.pop("_decode_graphs", None)  # captured graphs pin the kv / table / weight buffers
+        self.__dict__.pop("_prefill_graphs", None)
 
     def clear_kv_cache(self) -> None:
         self.mask_cache = None
@@ -139,6 +140,7 @@ class GPT(nn.Module):
             block.attn.kv_cache = None
         self._fused_plan = None
         self.__dict__.pop("_decode_graphs", None)  # captured graphs pin the kv / table / weight buffers
+        self.__dict__.pop("_prefill_graphs", None)
 
     # ------------------------------------------------------------------------------------------------------
     # fused decode step
@@ -151,6 +153,7 @@ class GPT(nn.Module):
         self.__dict__.pop("_seq_tables", None)
         self.__dict__.pop("_p2p", None)
         self.__dict__.pop("_decode_graphs", None)  # captured graphs pin the kv / table / weight buffers
+        self.__dict__.pop("_prefill_graphs", None)
         return super()._apply(fn, recurse)
 
     def fused_decode_ready(self, idx: Optional[torch.Tensor] = None) -> bool:

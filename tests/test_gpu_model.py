@@ -304,6 +304,21 @@ def test_sampling_path_in_graph(golden):
     cut = gb.generate(model, prompt, 30, temperature=0.0, eos_id=eos)
     first = next(i for i in range(6, 30) if int(greedy[i]) == eos)
     assert cut.tolist() == greedy[: first + 1].tolist()
+    # short prompts run their prefill as a captured graph (generate/base.py PrefillGraph): same tokens as the eager prefill, greedy
+    # and sampled (the graph's warm-up draws must not advance the Philox stream), also when replayed with another prompt
+    assert prompt.numel() <= gb.PREFILL_GRAPH_MAX_T and model.__dict__.get("_prefill_graphs")
+    prompt2 = (prompt + 3) % cfgd["vocab_size"]
+    seed_everything(77)
+    with_graph = [gb.generate(model, q, 30, temperature=t, top_k=k) for q, t, k in ((prompt, 0.0, None), (prompt2, 0.0, None), (prompt2, 0.8, 20), (prompt, 0.8, 20))]
+    keep = gb.PREFILL_GRAPH_MAX_T
+    try:
+        gb.PREFILL_GRAPH_MAX_T = 0
+        seed_everything(77)
+        eager = [gb.generate(model, q, 30, temperature=t, top_k=k) for q, t, k in ((prompt, 0.0, None), (prompt2, 0.0, None), (prompt2, 0.8, 20), (prompt, 0.8, 20))]
+    finally:
+        gb.PREFILL_GRAPH_MAX_T = keep
+    for a, b in zip(with_graph, eager):
+        assert torch.equal(a, b)
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (the one-GPU variant is tests/test_gpu_tp_shared.py)")
