@@ -30,6 +30,8 @@ struct GemmParams {
   __nv_bfloat16* y;           // (M, N)
   int64_t M, N, K;
   int qtype;
+  int ksplit;                 // > 1 (grids that would not fill the SMs): blockIdx.z owns a range of k-blocks and writes fp32 partial sums
+  float* partial;             // (ksplit, M, N) fp32, summed in split order by qgemm_splitk_reduce_kernel
 };
 
 constexpr int kGProducers = 512;            // 16 warps: 4 per scheduler, enough to hide the look-up latency
@@ -89,7 +91,10 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
   const uint32_t tiles_a = g_smem_u32(tiles);
   const uint32_t full0 = g_smem_u32(&s_bars[0]), empty0 = g_smem_u32(&s_bars[kGStages]), done_bar = g_smem_u32(&s_bars[2 * kGStages]);
   const int64_t n0 = (int64_t)blockIdx.x * kBN, m0 = (int64_t)blockIdx.y * (128 * MT);
-  const int nkb = (int)(p.K / kBK);
+  // split-K (short prompts: the output tiles alone would leave most SMs idle): this CTA's k-blocks are [kb0, kb0 + nkb)
+  const int nkb_all = (int)(p.K / kBK);
+  const int kb0 = (int)(((int64_t)nkb_all * blockIdx.z) / p.ksplit);
+  const int nkb = (int)(((int64_t)nkb_all * (blockIdx.z + 1)) / p.ksplit) - kb0;
   const bool int4 = p.qtype == B200_Q_INT4;
 
   if (tid == 0) {
@@ -129,7 +134,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
     for (int i = 0; i < kWLag; ++i) {
       qn[i] = make_uint2(0u, 0u);
       scn[i] = 0u;
-      if (wvalid && i < nkb) { qn[i] = ldg_stream_v2(wsrc + (int64_t)i * 32); scn[i] = ssrc[int4 ? (i >> 1) : i]; }
+      if (wvalid && i < nkb) { qn[i] = ldg_stream_v2(wsrc + (int64_t)(kb0 + i) * 32); scn[i] = ssrc[int4 ? ((kb0 + i) >> 1) : (kb0 + i)]; }
     }
     const uint32_t wdst0 = (uint32_t)(MT * kTileBytes) + sw128(wr, wh * 2), wdst1 = (uint32_t)(MT * kTileBytes) + sw128(wr, wh * 2 + 1);
     for (int kb = 0; kb < nkb; ++kb) {
@@ -143,7 +148,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
 #pragma unroll
         for (int mt = 0; mt < MT; ++mt)
           asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                       ::"r"(tiles_a + (uint32_t)(s * STAGE + mt * kTileBytes)), "l"(&tmap_x), "r"(kb * kBK), "r"((int)(m0 + mt * 128)), "r"(bar)
+                       ::"r"(tiles_a + (uint32_t)(s * STAGE + mt * kTileBytes)), "l"(&tmap_x), "r"((kb0 + kb) * kBK), "r"((int)(m0 + mt * 128)), "r"(bar)
                        : "memory");
       }
       // ---- weight tile: dequantise 16 codes -> 2 chunks of 8 bf16 ----------------------------------------------------
@@ -155,7 +160,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
         const int kn = kb + kWLag;
         qn[kWLag - 1] = make_uint2(0u, 0u);
         scn[kWLag - 1] = 0u;
-        if (wvalid && kn < nkb) { qn[kWLag - 1] = ldg_stream_v2(wsrc + (int64_t)kn * 32); scn[kWLag - 1] = ssrc[int4 ? (kn >> 1) : kn]; }
+        if (wvalid && kn < nkb) { qn[kWLag - 1] = ldg_stream_v2(wsrc + (int64_t)(kb0 + kn) * 32); scn[kWLag - 1] = ssrc[int4 ? ((kb0 + kn) >> 1) : (kb0 + kn)]; }
       }
       const uint32_t qw[2] = {q.x, q.y};
       if (int4) {
@@ -230,7 +235,14 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
               "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
             : "r"(taddr));
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        if (m < p.M) {
+        if (m < p.M && p.ksplit > 1) {
+          float* dst = p.partial + ((int64_t)blockIdx.z * p.M + m) * p.N;   // raw fp32 sums of this k range; bias and rounding in the reduce kernel
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const int64_t n = n0 + c0 + j;
+            if (n < p.N) *reinterpret_cast<uint4*>(dst + n) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          }
+        } else if (m < p.M) {
 #pragma unroll
           for (int j = 0; j < 32; j += 8) {
             const int64_t n = n0 + c0 + j;
@@ -254,6 +266,45 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
   if (warp == kGProducers / 32) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
   }
+}
+
+// y = bf16(sum over the k ranges, in range order, + bias): eight outputs per thread (N % 8 == 0)
+__global__ void __launch_bounds__(256) qgemm_splitk_reduce_kernel(const float* __restrict__ partial, const __nv_bfloat16* __restrict__ bias,
+                                                                  __nv_bfloat16* __restrict__ y, int64_t MN, int64_t N, int ksplit) {
+  griddep_launch();
+  griddep_wait();
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (i >= MN) return;
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+  for (int z = 0; z < ksplit; ++z) {
+    const float4 a = *reinterpret_cast<const float4*>(partial + (int64_t)z * MN + i);
+    const float4 b = *reinterpret_cast<const float4*>(partial + (int64_t)z * MN + i + 4);
+    acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w; acc[4] += b.x; acc[5] += b.y; acc[6] += b.z; acc[7] += b.w;
+  }
+  const int64_t n = i % N;
+  uint32_t o[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    float a = acc[2 * e], b = acc[2 * e + 1];
+    if (bias) { a += __bfloat162float(bias[n + 2 * e]); b += __bfloat162float(bias[n + 2 * e + 1]); }
+    o[e] = pack_bf16(a, b);
+  }
+  *reinterpret_cast<uint4*>(y + i) = make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+// k ranges for prompts whose (M tiles) x (N / 128) CTAs leave SMs idle (up to ~1000 tokens at N = 4096): enough ranges to fill ONE wave
+// (a second, partial wave costs more than the idle SMs of the first), at least one lap of the four-stage ring per range, and at
+// most 64 MB of fp32 partial sums
+static int gemm_ksplit(int64_t M, int64_t N, int64_t K) {
+  const int nkb = (int)(K / kBK);
+  const int64_t ctas = ((N + kBN - 1) / kBN) * ((M + (M > 128 ? 255 : 127)) / (M > 128 ? 256 : 128));
+  int64_t s = sm_count() / (ctas > 0 ? ctas : 1);
+  if (s > nkb / kGStages) s = nkb / kGStages;
+  if (s > 16) s = 16;
+  while (s > 1 && s * M * N * (int64_t)sizeof(float) > (64ll << 20)) --s;
+  return s < 1 ? 1 : (int)s;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -289,8 +340,11 @@ static cudaError_t launch_gemm(const GemmParams& p, cudaStream_t st) {
   if (enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(p.x), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
     return cudaErrorInvalidValue;
-  dim3 grid((unsigned)((p.N + kBN - 1) / kBN), (unsigned)((p.M + 128 * MT - 1) / (128 * MT)));
-  return launch(qgemm_tcgen05_kernel<MT>, grid, dim3(kGThreads), (size_t)smem, st, p, tmap);
+  dim3 grid((unsigned)((p.N + kBN - 1) / kBN), (unsigned)((p.M + 128 * MT - 1) / (128 * MT)), (unsigned)p.ksplit);
+  cudaError_t e = launch(qgemm_tcgen05_kernel<MT>, grid, dim3(kGThreads), (size_t)smem, st, p, tmap);
+  if (e != cudaSuccess || p.ksplit == 1) return e;
+  const int64_t MN = p.M * p.N;
+  return launch(qgemm_splitk_reduce_kernel, dim3((unsigned)((MN / 8 + 255) / 256)), dim3(256), (size_t)0, st, (const float*)p.partial, p.bias, p.y, MN, p.N, p.ksplit);
 }
 
 }  // namespace b200
@@ -300,8 +354,10 @@ using namespace b200;
 extern "C" {
 
 size_t b200_qgemm_workspace_bytes(int64_t M, int64_t N, int64_t K) {
-  (void)M; (void)N; (void)K;
-  return 0;  // accumulators live in tensor memory; nothing is staged in HBM
+  // accumulators live in tensor memory; only a launch split over k ranges (short prompts: too few output tiles for the SMs) stages fp32 partial sums
+  if (M <= 0 || N <= 0 || K < kBK) return 0;
+  const int s = gemm_ksplit(M, N, K);
+  return s > 1 ? (size_t)s * (size_t)M * (size_t)N * sizeof(float) : 0;
 }
 
 int b200_qgemm(const b200_qgemm_args* a, b200_stream_t stream) {
@@ -325,6 +381,12 @@ int b200_qgemm(const b200_qgemm_args* a, b200_stream_t stream) {
   p.bias = reinterpret_cast<const __nv_bfloat16*>(a->bias);
   p.y = reinterpret_cast<__nv_bfloat16*>(a->y);
   p.M = a->M; p.N = a->N; p.K = a->K; p.qtype = a->qtype;
+  // split-K only when the caller provided the workspace b200_qgemm_workspace_bytes asks for (none: one k range, as before)
+  p.ksplit = gemm_ksplit(a->M, a->N, a->K);
+  if (p.ksplit > 1 && (a->workspace == nullptr || a->workspace_bytes < (size_t)p.ksplit * a->M * a->N * sizeof(float) ||
+                       (reinterpret_cast<uintptr_t>(a->workspace) & 15)))
+    p.ksplit = 1;
+  p.partial = reinterpret_cast<float*>(a->workspace);
   cudaStream_t st = (cudaStream_t)stream;
   const cudaError_t e = a->M > 128 ? launch_gemm<2>(p, st) : launch_gemm<1>(p, st);
   if (e != cudaSuccess) {

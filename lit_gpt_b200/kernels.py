@@ -383,8 +383,10 @@ def qgemm(x: torch.Tensor, packed: torch.Tensor, scale: torch.Tensor, N: int, K:
     if x.numel() != M * K:
         raise C.B200Error("qgemm: x does not hold whole rows of length K")
     y = out if out is not None else torch.empty(tuple(x.shape[:-1]) + (N,), dtype=torch.bfloat16, device=x.device)
+    need = C.load().b200_qgemm_workspace_bytes(M, N, K)   # fp32 partial sums of a one-tile prompt split over k ranges; 0 otherwise
+    ws = _ws("qgemm", x.device, need) if need else None
     args = C.QGemmArgs(packed=packed.data_ptr(), scale=scale.data_ptr(), qtype=QTYPES[quant_type], blocksize=blocksize, M=M, N=N, K=K,
-                       x=x.data_ptr(), bias=C.ptr(bias), y=y.data_ptr(), workspace=None, workspace_bytes=0)
+                       x=x.data_ptr(), bias=C.ptr(bias), y=y.data_ptr(), workspace=C.ptr(ws), workspace_bytes=0 if ws is None else ws.numel())
     C.check(C.load().b200_qgemm(ctypes.byref(args), C.stream_ptr(x.device)), "qgemm")
     return y
 

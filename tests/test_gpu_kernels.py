@@ -645,13 +645,21 @@ def test_qgemv_tiled_onehot_reads_dequantised_column(K):
 
 # ---- prefill GEMM on tcgen05 / TMEM (csrc/qgemm.cu) ---------------------------------------------------------------
 @pytest.mark.parametrize("qt", ["nf4", "fp4", "int4"])
-@pytest.mark.parametrize("M,N,Kdim", [(128, 128, 128), (17, 8, 128), (256, 256, 512), (300, 520, 1024), (129, 4096, 4096), (1000, 344, 11008)])
+@pytest.mark.parametrize("M,N,Kdim", [(128, 128, 128), (17, 8, 128), (256, 256, 512), (300, 520, 1024), (129, 4096, 4096), (1000, 344, 11008),
+                                      (64, 4096, 4096), (128, 4096, 11008), (17, 1000, 5120), (100, 12288, 4096), (200, 4096, 4096), (520, 2048, 4096)])
 def test_qgemm_tcgen05(K, qt, M, N, Kdim):
     w, _, packed, scale, bs, deq = _gemv_case(K, N, Kdim, 1, qt, seed=M + N)
     x = _randw((M, Kdim), 5, std=1.0)
-    bias = _randw((N,), 6, std=0.5) if M == 300 else None
+    bias = _randw((N,), 6, std=0.5) if M in (300, 100, 17) else None
     y = K.qgemm(x.cuda(), packed, scale, N, Kdim, qt, bs, bias=None if bias is None else bias.cuda())
     assert y.shape == (M, N)
+    from lit_gpt_b200 import _cabi as C
+    need = C.load().b200_qgemm_workspace_bytes(M, N, Kdim)   # short prompts are split over k ranges: fp32 partial sums, summed in range order
+    if need:
+        assert need >= 2 * M * N * 4
+        assert torch.equal(y, K.qgemm(x.cuda(), packed, scale, N, Kdim, qt, bs, bias=None if bias is None else bias.cuda())), "not deterministic"
+    if M <= 256 and Kdim >= 512 and N <= 128 * 74:
+        assert need > 0, "output tiles fill less than half the SMs: the launch must be split over k ranges"
     # the weight tile the tensor core sees is bf16_rn(dequant): same operands as the reference's dequantize + F.linear,
     # so the only difference to a library GEMM on those operands is the fp32 accumulation order
     wb = deq.to(torch.bfloat16)
