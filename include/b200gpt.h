@@ -331,6 +331,9 @@ typedef struct b200_qgemm_args {
 } b200_qgemm_args;
 size_t b200_qgemm_workspace_bytes(int64_t M, int64_t N, int64_t K);
 int b200_qgemm(const b200_qgemm_args* args, b200_stream_t stream);
+/* tuning: mt3 = 1 (default): prompts of more than 512 tokens share each dequantised weight tile among 384 tokens (three 128-row
+ * accumulators in tensor memory, three 64 KB stages); 0: 256 tokens as in round 1 */
+int b200_qgemm_tune(int mt3);
 
 /* ---- bnb.int8: LLM.int8() inference Linear (replaces bitsandbytes.nn.Linear8bitLt(has_fp16_weights=False,
  *      threshold=6.0) installed by BitsandbytesPrecision("int8") at generate/base.py:129-134; arithmetic restated in

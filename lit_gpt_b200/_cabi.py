@@ -123,6 +123,7 @@ _SIGNATURES = {
                             c_void_p]),
     "b200_qgemm_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int64]),
     "b200_qgemm": (c_int, [ctypes.POINTER(QGemmArgs), c_void_p]),
+    "b200_qgemm_tune": (c_int, [c_int]),
 }
 
 _lib = None

@@ -81,7 +81,8 @@ template <int MT>
 __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x) {
   extern __shared__ __align__(1024) uint8_t g_smem[];
   constexpr int STAGE = (MT + 1) * kTileBytes;      // MT activation tiles + 1 weight tile
-  constexpr int TMEM_COLS = 128 * MT;
+  constexpr int TMEM_COLS = MT <= 2 ? 128 * MT : 512;   // a power of two (MT = 3: 384 accumulator columns of 512)
+  constexpr int NSTAGE = MT <= 2 ? kGStages : 3;          // MT = 3: 64 KB stages, three of them fit
   __shared__ __align__(8) uint64_t s_bars[2 * kGStages + 1];
   __shared__ uint32_t s_tmem;
   __shared__ float s_code[16 * 32];                 // fp32 code book, one copy per lane (conflict-free look-ups)
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
   const bool int4 = p.qtype == B200_Q_INT4;
 
   if (tid == 0) {
-    for (int s = 0; s < kGStages; ++s) { g_mbar_init(full0 + s * 8, kGProducers / 32 + 1); g_mbar_init(empty0 + s * 8, 1); }
+    for (int s = 0; s < NSTAGE; ++s) { g_mbar_init(full0 + s * 8, kGProducers / 32 + 1); g_mbar_init(empty0 + s * 8, 1); }
     g_mbar_init(done_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -138,8 +139,8 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
     }
     const uint32_t wdst0 = (uint32_t)(MT * kTileBytes) + sw128(wr, wh * 2), wdst1 = (uint32_t)(MT * kTileBytes) + sw128(wr, wh * 2 + 1);
     for (int kb = 0; kb < nkb; ++kb) {
-      const int s = kb % kGStages;
-      if (kb >= kGStages) g_mbar_wait(empty0 + s * 8, ((kb / kGStages) - 1) & 1);
+      const int s = kb % NSTAGE;
+      if (kb >= NSTAGE) g_mbar_wait(empty0 + s * 8, ((kb / NSTAGE) - 1) & 1);
       const uint32_t st_a = tiles_a + (uint32_t)(s * STAGE);   // shared-window address: explicit st.shared, not generic stores
       // ---- activation tiles: MT boxes of 128 rows x 64 k by TMA, issued by one thread ------------------------------
       if (tid == 0) {
@@ -198,8 +199,8 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
   } else if (lane == 0) {
     // =========================================== MMA ISSUER =====================================================
     for (int kb = 0; kb < nkb; ++kb) {
-      const int s = kb % kGStages;
-      g_mbar_wait(full0 + s * 8, (kb / kGStages) & 1);
+      const int s = kb % NSTAGE;
+      g_mbar_wait(full0 + s * 8, (kb / NSTAGE) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t sa = tiles_a + s * STAGE;
       const uint64_t db = umma_desc_sw128(sa + MT * kTileBytes);
@@ -294,12 +295,15 @@ __global__ void __launch_bounds__(256) qgemm_splitk_reduce_kernel(const float* _
   *reinterpret_cast<uint4*>(y + i) = make_uint4(o[0], o[1], o[2], o[3]);
 }
 
+static std::atomic<int> g_gemm_mt3{1};   // development switch (b200_qgemm_tune)
+
 // k ranges for prompts whose (M tiles) x (N / 128) CTAs leave SMs idle (up to ~1000 tokens at N = 4096): enough ranges to fill ONE wave
 // (a second, partial wave costs more than the idle SMs of the first), at least one lap of the four-stage ring per range, and at
 // most 64 MB of fp32 partial sums
 static int gemm_ksplit(int64_t M, int64_t N, int64_t K) {
   const int nkb = (int)(K / kBK);
-  const int64_t ctas = ((N + kBN - 1) / kBN) * ((M + (M > 128 ? 255 : 127)) / (M > 128 ? 256 : 128));
+  const int64_t mtile = M > 512 && g_gemm_mt3.load() ? 384 : M > 128 ? 256 : 128;
+  const int64_t ctas = ((N + kBN - 1) / kBN) * ((M + mtile - 1) / mtile);
   int64_t s = sm_count() / (ctas > 0 ? ctas : 1);
   if (s > nkb / kGStages) s = nkb / kGStages;
   if (s > 16) s = 16;
@@ -322,7 +326,7 @@ static EncodeTiledFn encode_tiled() {
 
 template <int MT>
 static cudaError_t launch_gemm(const GemmParams& p, cudaStream_t st) {
-  constexpr int smem = kGStages * (MT + 1) * kTileBytes + 1024;
+  constexpr int smem = (MT <= 2 ? kGStages : 3) * (MT + 1) * kTileBytes + 1024;
   static PerDeviceOnce once;
   if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(qgemm_tcgen05_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -352,6 +356,8 @@ static cudaError_t launch_gemm(const GemmParams& p, cudaStream_t st) {
 using namespace b200;
 
 extern "C" {
+
+int b200_qgemm_tune(int mt3) { g_gemm_mt3 = mt3 ? 1 : 0; return B200_OK; }
 
 size_t b200_qgemm_workspace_bytes(int64_t M, int64_t N, int64_t K) {
   // accumulators live in tensor memory; only a launch split over k ranges (short prompts: too few output tiles for the SMs) stages fp32 partial sums
@@ -388,7 +394,8 @@ int b200_qgemm(const b200_qgemm_args* a, b200_stream_t stream) {
     p.ksplit = 1;
   p.partial = reinterpret_cast<float*>(a->workspace);
   cudaStream_t st = (cudaStream_t)stream;
-  const cudaError_t e = a->M > 128 ? launch_gemm<2>(p, st) : launch_gemm<1>(p, st);
+  // tokens per dequantised weight tile: 128, 256, or 384 for long prompts (the CUDA-core dequantisation is the bound: §5.4)
+  const cudaError_t e = a->M > 512 && g_gemm_mt3.load() ? launch_gemm<3>(p, st) : a->M > 128 ? launch_gemm<2>(p, st) : launch_gemm<1>(p, st);
   if (e != cudaSuccess) {
     set_error("b200_qgemm: launch failed: %s", cudaGetErrorString(e));
     return B200_ERR_CUDA;

@@ -391,6 +391,11 @@ def qgemm(x: torch.Tensor, packed: torch.Tensor, scale: torch.Tensor, N: int, K:
     return y
 
 
+def qgemm_tune(mt3: bool = True) -> None:
+    """development switch: 384-token tiles for long prompts (default) or the 256-token tiles of round 1"""
+    C.check(C.load().b200_qgemm_tune(1 if mt3 else 0), "qgemm_tune")
+
+
 def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float = 1e-5, delta: Optional[torch.Tensor] = None,
             sum_out: Optional[torch.Tensor] = None) -> torch.Tensor:
     C.require_cuda(x, weight)

@@ -646,7 +646,7 @@ def test_qgemv_tiled_onehot_reads_dequantised_column(K):
 # ---- prefill GEMM on tcgen05 / TMEM (csrc/qgemm.cu) ---------------------------------------------------------------
 @pytest.mark.parametrize("qt", ["nf4", "fp4", "int4"])
 @pytest.mark.parametrize("M,N,Kdim", [(128, 128, 128), (17, 8, 128), (256, 256, 512), (300, 520, 1024), (129, 4096, 4096), (1000, 344, 11008),
-                                      (64, 4096, 4096), (128, 4096, 11008), (17, 1000, 5120), (100, 12288, 4096), (200, 4096, 4096), (520, 2048, 4096)])
+                                      (64, 4096, 4096), (128, 4096, 11008), (17, 1000, 5120), (100, 12288, 4096), (200, 4096, 4096), (520, 2048, 4096), (1153, 1024, 2048)])
 def test_qgemm_tcgen05(K, qt, M, N, Kdim):
     w, _, packed, scale, bs, deq = _gemv_case(K, N, Kdim, 1, qt, seed=M + N)
     x = _randw((M, Kdim), 5, std=1.0)

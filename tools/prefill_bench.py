@@ -26,6 +26,7 @@ def main() -> None:
     ap.add_argument("--tokens", type=int, default=4096)
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--layers", type=int, default=None)
+    ap.add_argument("--mt3", type=int, default=1, help="0: 256-token GEMM tiles (round 1) instead of 384")
     args = ap.parse_args()
 
     import bench
@@ -33,6 +34,7 @@ def main() -> None:
     from lit_gpt_b200 import kernels as K
     from lit_gpt_b200.fabric import Fabric
 
+    K.qgemm_tune(bool(args.mt3))
     fabric = Fabric(devices=1, plugins=QuantPrecision(args.qt, torch.bfloat16))
     T = args.tokens
     model, cfg = bench.build_random_model(args.model, args.qt, T, 1, fabric, n_layer=args.layers)
