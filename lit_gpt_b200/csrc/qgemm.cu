@@ -165,30 +165,38 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
       }
       const uint32_t qw[2] = {q.x, q.y};
       if (int4) {
+        // bf16_rn(scale * (q - zero)) with three instructions per code: the nibble is moved to the top four mantissa bits of 16.0f
+        // (SHF + LOP3: f = 16 + q exactly, five significant bits), then ONE FFMA scale * f - scale * (16 + zero): both products are
+        // exact in fp32 (11-bit fp16 scale x 6-bit integer), so the result is the exact scale * (q - zero), as before -- without the
+        // quarter-rate I2F per code that bound this loop
         const __half2 h2 = *reinterpret_cast<const __half2*>(&sc);
-        const float scale = __low2float(h2), zero = __high2float(h2);
+        const float scale = __low2float(h2);
+        const float c0 = -scale * (16.0f + __high2float(h2));
+        auto deq = [&](uint32_t w, int e) -> float {   // element e (bits 4e .. 4e + 3) of word w
+          const uint32_t sh = e <= 4 ? w << (19 - 4 * e) : w >> (4 * e - 19);
+          return fmaf(scale, __uint_as_float((sh & 0x00780000u) | 0x41800000u), c0);
+        };
 #pragma unroll
         for (int j = 0; j < 2; ++j) {  // word j = k [16h + 8j, +8), element e in bits 4e
           uint32_t o[4];
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float a = scale * ((float)((qw[j] >> (8 * e)) & 15u) - zero);
-            const float b = scale * ((float)((qw[j] >> (8 * e + 4)) & 15u) - zero);
-            o[e] = pack_bf16(a, b);
-          }
+          for (int e = 0; e < 4; ++e) o[e] = pack_bf16(deq(qw[j], 2 * e), deq(qw[j], 2 * e + 1));
           asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(st_a + (j ? wdst1 : wdst0)), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
         }
       } else {
+        // bf16_rn(code_fp32 * absmax_fp32): look-up offset = nibble << 7 | lane << 2 from the table's (link-time constant) address:
+        // SHF + LOP3 + LDS per code
         const float am = __uint_as_float(sc);
-        const float* code = s_code + lane;
+        const uint32_t lane4 = (uint32_t)lane * 4u;
+        auto deq = [&](uint32_t w, int bit) -> float {   // the nibble at bits bit .. bit + 3 of word w
+          const uint32_t sh = bit <= 7 ? w << (7 - bit) : w >> (bit - 7);
+          return *reinterpret_cast<const float*>(reinterpret_cast<const char*>(s_code) + ((sh & 0x780u) | lane4)) * am;
+        };
 #pragma unroll
         for (int j = 0; j < 2; ++j) {  // word j = bytes 4j..4j+3 = k [16h + 8j, +8); even element in the HIGH nibble
           uint32_t o[4];
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const uint32_t byte = (qw[j] >> (8 * e)) & 255u;
-            o[e] = pack_bf16(code[(byte >> 4) * 32] * am, code[(byte & 15u) * 32] * am);
-          }
+          for (int e = 0; e < 4; ++e) o[e] = pack_bf16(deq(qw[j], 8 * e + 4), deq(qw[j], 8 * e));
           asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(st_a + (j ? wdst1 : wdst0)), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
         }
       }

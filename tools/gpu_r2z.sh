@@ -1,6 +1,4 @@
 #!/bin/bash
 timeout 300 python -u -m pytest tests/test_gpu_kernels.py -x -q -m gpu --timeout 60 -k "qgemm" 2>&1 | grep -E "passed|failed|Error|assert" | tail -5
-for mt in 0 1; do
-timeout 300 python tools/prefill_bench.py --mt3 $mt 2>&1 | grep -v "^DEBUG\|Warn\|warn" | tail -1
-timeout 300 python tools/prefill_bench.py --mt3 $mt --model Llama-2-7b-hf --qt nf4 2>&1 | grep -v "^DEBUG\|Warn\|warn" | tail -1
-done
+timeout 300 python tools/prefill_bench.py 2>&1 | grep -v "^DEBUG\|Warn\|warn" | tail -1
+timeout 300 python tools/prefill_bench.py --model Llama-2-7b-hf --qt nf4 2>&1 | grep -v "^DEBUG\|Warn\|warn" | tail -1
