@@ -77,7 +77,7 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {  // arrives on `bar`
 // byte offset of the 16-byte chunk `c` (0..7) of row `r` inside a 128-row K-major SWIZZLE_128B tile
 __device__ __forceinline__ uint32_t sw128(int r, int c) { return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4)); }
 
-template <int MT>
+template <int MT, bool INT4>
 __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x) {
   extern __shared__ __align__(1024) uint8_t g_smem[];
   constexpr int STAGE = (MT + 1) * kTileBytes;      // MT activation tiles + 1 weight tile
@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
   const int nkb_all = (int)(p.K / kBK);
   const int kb0 = (int)(((int64_t)nkb_all * blockIdx.z) / p.ksplit);
   const int nkb = (int)(((int64_t)nkb_all * (blockIdx.z + 1)) / p.ksplit) - kb0;
-  const bool int4 = p.qtype == B200_Q_INT4;
+  constexpr bool int4 = INT4;
 
   if (tid == 0) {
     for (int s = 0; s < NSTAGE; ++s) { g_mbar_init(full0 + s * 8, kGProducers / 32 + 1); g_mbar_init(empty0 + s * 8, 1); }
@@ -135,13 +135,18 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
     for (int i = 0; i < kWLag; ++i) {
       qn[i] = make_uint2(0u, 0u);
       scn[i] = 0u;
-      if (wvalid && i < nkb) { qn[i] = ldg_stream_v2(wsrc + (int64_t)(kb0 + i) * 32); scn[i] = ssrc[int4 ? ((kb0 + i) >> 1) : (kb0 + i)]; }
+      if (i < nkb) { qn[i] = ldg_stream_v2(wsrc + (int64_t)(kb0 + i) * 32); scn[i] = ssrc[int4 ? ((kb0 + i) >> 1) : (kb0 + i)]; }
     }
     const uint32_t wdst0 = (uint32_t)(MT * kTileBytes) + sw128(wr, wh * 2), wdst1 = (uint32_t)(MT * kTileBytes) + sw128(wr, wh * 2 + 1);
+    // running state instead of per-iteration index arithmetic (the loop is bound by its instruction count: 139 -> ~105 per k-block):
+    // ring slot / parity, the packed-weight pointer and the k-block index of the look-ahead load (rows past N read row 0: in bounds)
+    const uint8_t* wp = wsrc + (int64_t)(kb0 + kWLag) * 32;
+    int kq = kb0 + kWLag;                 // absolute k-block of the next look-ahead load
+    int s = 0;
+    uint32_t eph = 1;                     // parity of the EMPTY phase to wait for (first lap: passes at once)
+    uint32_t st_a = tiles_a;              // shared-window address of the current stage
     for (int kb = 0; kb < nkb; ++kb) {
-      const int s = kb % NSTAGE;
-      if (kb >= NSTAGE) g_mbar_wait(empty0 + s * 8, ((kb / NSTAGE) - 1) & 1);
-      const uint32_t st_a = tiles_a + (uint32_t)(s * STAGE);   // shared-window address: explicit st.shared, not generic stores
+      g_mbar_wait(empty0 + s * 8, eph);
       // ---- activation tiles: MT boxes of 128 rows x 64 k by TMA, issued by one thread ------------------------------
       if (tid == 0) {
         const uint32_t bar = full0 + s * 8;
@@ -149,7 +154,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
 #pragma unroll
         for (int mt = 0; mt < MT; ++mt)
           asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                       ::"r"(tiles_a + (uint32_t)(s * STAGE + mt * kTileBytes)), "l"(&tmap_x), "r"((kb0 + kb) * kBK), "r"((int)(m0 + mt * 128)), "r"(bar)
+                       ::"r"(st_a + (uint32_t)(mt * kTileBytes)), "l"(&tmap_x), "r"((kb0 + kb) * kBK), "r"((int)(m0 + mt * 128)), "r"(bar)
                        : "memory");
       }
       // ---- weight tile: dequantise 16 codes -> 2 chunks of 8 bf16 ----------------------------------------------------
@@ -157,12 +162,8 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
       const uint32_t sc = scn[0];
 #pragma unroll
       for (int i = 0; i + 1 < kWLag; ++i) { qn[i] = qn[i + 1]; scn[i] = scn[i + 1]; }
-      {
-        const int kn = kb + kWLag;
-        qn[kWLag - 1] = make_uint2(0u, 0u);
-        scn[kWLag - 1] = 0u;
-        if (wvalid && kn < nkb) { qn[kWLag - 1] = ldg_stream_v2(wsrc + (int64_t)(kb0 + kn) * 32); scn[kWLag - 1] = ssrc[int4 ? ((kb0 + kn) >> 1) : (kb0 + kn)]; }
-      }
+      if (kb + kWLag < nkb) { qn[kWLag - 1] = ldg_stream_v2(wp); scn[kWLag - 1] = ssrc[int4 ? (kq >> 1) : kq]; }
+      wp += 32; ++kq;
       const uint32_t qw[2] = {q.x, q.y};
       if (int4) {
         // bf16_rn(scale * (q - zero)) with three instructions per code: the nibble is moved to the top four mantissa bits of 16.0f
@@ -203,12 +204,15 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // generic-proxy writes -> visible to the tensor core
       __syncwarp();
       if (lane == 0) g_mbar_arrive(full0 + s * 8);                       // weight tile of kb
+      st_a += STAGE;
+      if (++s == NSTAGE) { s = 0; eph ^= 1u; st_a = tiles_a; }
     }
   } else if (lane == 0) {
     // =========================================== MMA ISSUER =====================================================
+    int s = 0;
+    uint32_t fph = 0;
     for (int kb = 0; kb < nkb; ++kb) {
-      const int s = kb % NSTAGE;
-      g_mbar_wait(full0 + s * 8, (kb / NSTAGE) & 1);
+      g_mbar_wait(full0 + s * 8, fph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t sa = tiles_a + s * STAGE;
       const uint64_t db = umma_desc_sw128(sa + MT * kTileBytes);
@@ -220,6 +224,7 @@ __global__ void __launch_bounds__(kGThreads, 1) qgemm_tcgen05_kernel(const GemmP
           umma_bf16(tmem + mt * 128, da + 2 * k, db + 2 * k, (kb | k) != 0);
       }
       umma_commit(empty0 + s * 8);   // stage reusable once these MMAs have read it (implies fence::before_thread_sync)
+      if (++s == NSTAGE) { s = 0; fph ^= 1u; }
     }
     umma_commit(done_bar);           // accumulators complete
   }
@@ -332,12 +337,12 @@ static EncodeTiledFn encode_tiled() {
   return fn;
 }
 
-template <int MT>
-static cudaError_t launch_gemm(const GemmParams& p, cudaStream_t st) {
+template <int MT, bool INT4>
+static cudaError_t launch_gemm_q(const GemmParams& p, cudaStream_t st) {
   constexpr int smem = (MT <= 2 ? kGStages : 3) * (MT + 1) * kTileBytes + 1024;
   static PerDeviceOnce once;
   if (once.need()) {
-    cudaError_t e = cudaFuncSetAttribute(qgemm_tcgen05_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute(qgemm_tcgen05_kernel<MT, INT4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     once.done();
   }
@@ -353,10 +358,15 @@ static cudaError_t launch_gemm(const GemmParams& p, cudaStream_t st) {
           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
     return cudaErrorInvalidValue;
   dim3 grid((unsigned)((p.N + kBN - 1) / kBN), (unsigned)((p.M + 128 * MT - 1) / (128 * MT)), (unsigned)p.ksplit);
-  cudaError_t e = launch(qgemm_tcgen05_kernel<MT>, grid, dim3(kGThreads), (size_t)smem, st, p, tmap);
+  cudaError_t e = launch(qgemm_tcgen05_kernel<MT, INT4>, grid, dim3(kGThreads), (size_t)smem, st, p, tmap);
   if (e != cudaSuccess || p.ksplit == 1) return e;
   const int64_t MN = p.M * p.N;
   return launch(qgemm_splitk_reduce_kernel, dim3((unsigned)((MN / 8 + 255) / 256)), dim3(256), (size_t)0, st, (const float*)p.partial, p.bias, p.y, MN, p.N, p.ksplit);
+}
+
+template <int MT>
+static cudaError_t launch_gemm(const GemmParams& p, cudaStream_t st) {
+  return p.qtype == B200_Q_INT4 ? launch_gemm_q<MT, true>(p, st) : launch_gemm_q<MT, false>(p, st);
 }
 
 }  // namespace b200
