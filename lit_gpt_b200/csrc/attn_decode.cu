@@ -150,9 +150,10 @@ int b200_attn_decode(const b200_attn_decode_args* a, b200_stream_t stream) {
     // many sequences x heads over a long cache (13B, batch 16, 2048 positions: 640 CTAs of 1 MB each): three key ranges per (sequence,
     // head) still pay -- 136 -> 120 us per layer, 4.9 -> 5.6 TB/s (tools/attn_bench.py --splits) -- the last wave is shorter
     if (!gqa && nsplit < 3 && a->max_seq >= 3 * 512) nsplit = 3;
-    // a cache of at most 64 positions: one CTA per (sequence, head) without the cluster merge, 4.4 instead of 5.7 us per launch (equal at
-    // 100 positions, the split wins from ~200 on: tools/attn_bench.py --splits)
-    if (!gqa && a->max_seq <= 64) nsplit = 1;
+    // a cache of at most 128 positions: one CTA per (sequence, head) without the cluster merge -- 4.3 / 4.7 / 5.8 / 5.9 us at 27 / 60 / 100 /
+    // 112 filled positions against 4.3 (5.7 clustered) / 5.5 / 5.9 / 5.9; the split wins from ~150 on (7.3 vs 6.2 us at 176):
+    // tools/attn_bench.py --splits
+    if (!gqa && a->max_seq <= 128) nsplit = 1;
     // scalar kernel: cap at the portable cluster size so that the splits merge through distributed shared memory (the
     // tensor-core kernel measured the same with 9..16 workspace-merged splits as with 8 clustered ones: not capped)
     if (!gqa && !force_scalar && nsplit > 8) nsplit = 8;

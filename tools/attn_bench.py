@@ -18,7 +18,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 SHAPES = [  # name, H, G, ctx, B
-    ("7b ctx27", 32, 32, 27, 1), ("7b ctx100", 32, 32, 100, 1), ("7b ctx272", 32, 32, 272, 1), ("7b ctx2048", 32, 32, 2048, 1), ("13b ctx2048", 40, 40, 2048, 1), ("13b ctx2048 b4", 40, 40, 2048, 4),
+    ("7b ctx27", 32, 32, 27, 1), ("7b ctx60", 32, 32, 60, 1), ("7b ctx100", 32, 32, 100, 1), ("7b ctx112", 32, 32, 112, 1), ("7b ctx176", 32, 32, 176, 1), ("7b ctx272", 32, 32, 272, 1), ("7b ctx2048", 32, 32, 2048, 1), ("13b ctx2048", 40, 40, 2048, 1), ("13b ctx2048 b4", 40, 40, 2048, 4),
     ("13b ctx2048 b16", 40, 40, 2048, 16), ("mistral ctx4096", 32, 8, 4096, 1), ("70b tp2 ctx2048", 32, 4, 2048, 1), ("70b tp8 ctx2048", 8, 1, 2048, 1),
 ]
 
