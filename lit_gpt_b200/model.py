@@ -15,6 +15,7 @@ What differs is what runs underneath on a B200:
 from __future__ import annotations
 
 import math
+import os
 from typing import Any, List, Optional, Tuple
 
 import torch
@@ -26,7 +27,7 @@ from .config import Config
 from .quant import QLinear
 
 # batched decode with more rows than this runs RMSNorm as its own launch instead of in the GEMV prologue (see GPT._fused_decode)
-SPLIT_NORM_ROWS = int(__import__("os").environ.get("B200_SPLIT_NORM_ROWS", "8"))
+SPLIT_NORM_ROWS = int(os.environ.get("B200_SPLIT_NORM_ROWS", "8"))
 
 FUSED_HEAD_SIZES = (64, 128)
 
@@ -208,7 +209,6 @@ class GPT(nn.Module):
             return st or None
         if torch.cuda.is_current_stream_capturing():
             return None
-        import os
 
         from .p2p import PeerComm
 
@@ -447,7 +447,6 @@ class GPT(nn.Module):
             else:
                 logits = lin(head, x, delta=pending, norm_weight=self.transformer.ln_f.weight, norm_eps=eps)
             return logits.view(B, 1, -1)
-        import os
 
         a0 = blocks[0].attn.attn if blocks else None
         # EXPERIMENT, off by default (B200_FUSE_ATTN_MAX_SEQ=1024 enables it): the attention step fused into the QKV GEMV's
