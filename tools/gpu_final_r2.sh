@@ -1,18 +1,15 @@
 #!/bin/bash
-# round-2 final validation: what the driver runs at round end (GPU tests, smoke, the bench line, the reference arm) + refreshed records
+# round-2 final validation: what the driver runs at round end (GPU tests, smoke, the bench line) + a refreshed launch list of the headline step
 set -u
 mkdir -p gpurun_out/final gpurun_out/records
 timeout 1200 python -m pytest tests/ -x -q -m gpu --timeout 300 > gpurun_out/final/pytest_gpu.log 2>&1; echo "pytest -m gpu rc=$?"; grep -v "^DEBUG\|Deprec\|warnings.warn" gpurun_out/final/pytest_gpu.log | tail -3
 timeout 200 python -c "import __graft_entry__ as g; g.smoke(); print('__SMOKE_OK__')" > gpurun_out/final/smoke.log 2>&1; echo "smoke rc=$?"; grep -v "^DEBUG" gpurun_out/final/smoke.log | tail -2
 timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/final/bench_20.json 2> gpurun_out/final/bench_20.err; echo "bench 20 rc=$?"
-timeout 600 python bench.py > gpurun_out/final/bench_256.json 2> gpurun_out/final/bench_256.err; echo "bench 256 rc=$?"
-timeout 600 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/final/bench_ref_20.json 2> gpurun_out/final/bench_ref_20.err; echo "reference arm rc=$?"
-for WL in llama2-13b-int4-bs16-ctx2048; do
-  timeout 300 python bench.py --no-cpu-baseline --steps 64 --warmup 8 --workload $WL > gpurun_out/records/$WL.json 2> gpurun_out/records/$WL.err; echo "$WL rc=$?"
-done
+KRE='regex:qgemv|attn_|argmax|embedding|sample|rmsnorm|rope_kv|qgemm'
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KRE" --launch-skip 2000 -c 326 --csv --log-file gpurun_out/records/launches_r02.csv python bench.py --no-cpu-baseline --steps 4 --warmup 3 > gpurun_out/records/ncu_launch.log 2>&1; echo "ncu launch list rc=$?"
 python - <<'P'
-import json,glob
-for f in ["final/bench_20","final/bench_256","final/bench_ref_20","records/llama2-13b-int4-bs16-ctx2048"]:
+import json
+for f in ["final/bench_20"]:
     try:
         d=json.loads(open(f"gpurun_out/{f}.json").read().strip().split("\n")[-1])
         r=d.get("roofline") or {}
